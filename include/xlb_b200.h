@@ -1,0 +1,117 @@
+/*
+ * xlb_b200.h -- C ABI of libxlb_b200.so: hand-written sm_100a kernels for the per-timestep LBM
+ * update of XLB (hsalehipour/XLB), the path BASELINE.json:north_star names.
+ *
+ * The reference is 100% Python (JAX / Warp JIT); it has NO FFI of its own, so every entry point
+ * below cites the reference *operator* it replaces (file:line relative to the reference tree).
+ * The reference-side binding a maintainer would add is the ctypes stub shown in INTEGRATION.md.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a positive cudaError_t or a negative XLB_E* code;
+ *     xlb_last_error() gives the message of the last failure on the calling thread;
+ *   - all data pointers are BORROWED device pointers (e.g. torch ``tensor.data_ptr()``); nothing
+ *     is retained after the call returns; kernels are enqueued on ``stream`` (a cudaStream_t
+ *     passed as void*; NULL = legacy default stream) and the call does not synchronise;
+ *   - fields are C-contiguous [cardinality][nx][ny][nz] (z fastest), population l starts at
+ *     element l * q_stride (q_stride >= nx*ny*nz lets the host pad between populations);
+ *   - a 2-D lattice (D2Q9) field [q][NX][NY] is passed as nx=1, ny=NX, nz=NY;
+ *   - there is no CPU fallback anywhere in this library.
+ */
+#ifndef XLB_B200_H
+#define XLB_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define XLB_B200_ABI_VERSION 1
+
+/* element types (xlb/precision_policy.py:13-54) */
+enum { XLB_F16 = 0, XLB_F32 = 1, XLB_F64 = 2, XLB_U8 = 3 };
+/* collision models (xlb/operator/stepper/nse_stepper.py:79-87) */
+enum { XLB_BGK = 0, XLB_KBC = 1 };
+/* boundary-condition kinds (xlb/operator/boundary_condition/bc_*.py) */
+enum {
+    XLB_BC_NONE = 0,
+    XLB_BC_FULLWAY = 1,        /* bc_fullway_bounce_back.py:50-56   COLLISION step */
+    XLB_BC_EQUILIBRIUM = 2,    /* bc_equilibrium.py:72-80           STREAMING step */
+    XLB_BC_HALFWAY = 3,        /* bc_halfway_bounce_back.py:116-134 STREAMING step */
+    XLB_BC_DONOTHING = 4,      /* bc_do_nothing.py:50-54            STREAMING step */
+    XLB_BC_ZOUHE_VELOCITY = 5, /* bc_zouhe.py:290-304, bc_type="velocity" */
+    XLB_BC_ZOUHE_PRESSURE = 6, /* bc_zouhe.py:290-304, bc_type="pressure" */
+    XLB_BC_EXTRAPOLATION = 7   /* bc_extrapolation_outflow.py:106-145 (streaming apply + post-collision assemble) */
+};
+/* error codes */
+enum { XLB_EINVAL = -1, XLB_EUNSUPPORTED = -2, XLB_EALIGN = -3 };
+/* kernel variants for xlb_step (0 picks the tuned default) */
+enum { XLB_VARIANT_AUTO = 0, XLB_VARIANT_SCALAR = 1, XLB_VARIANT_VECTOR = 2, XLB_VARIANT_GENERIC = 3 };
+
+/* One row per BC id (index = the uint8 stored in bc_mask; row 0 unused).  Built on the host and
+ * uploaded once; replaces the per-stepper BC specialisation of nse_stepper.py:351-380. */
+typedef struct XlbBcEntry {
+    int32_t kind;         /* XLB_BC_* */
+    int32_t pv_dtype;     /* element type of pv (XLB_F16/F32/F64) */
+    int32_t normal[3];    /* ExtrapolationOutflowBC.normal, kernel axes (bc_extrapolation_outflow.py:78-92) */
+    int32_t reserved;
+    int64_t pv_stride[4]; /* strides (elements) of pv over (component, x, y, z); 0 = broadcast */
+    const void* pv;       /* Zou-He prescribed values, device pointer (bc_zouhe.py:119-120, 178-215) */
+    double table[27];     /* EQUILIBRIUM: feq_l (bc_equilibrium.py:74-76); HALFWAY: 6 w_l c_l.u_wall (bc_halfway_bounce_back.py:123-128) */
+} XlbBcEntry;
+
+/* Geometry + precision of one local block of the lattice. */
+typedef struct XlbDomain {
+    int32_t d, q;                      /* lattice: (2,9) (3,19) (3,27)  (xlb/velocity_set/*.py) */
+    int32_t nx, ny, nz;                /* allocated extents (kernel axes; ghost planes included) */
+    int32_t x_periodic;                /* 1: pull wraps in x (single block); 0: planes x_begin-1 / x_end exist (halo) */
+    int32_t compute_dtype, store_dtype;/* precision policy (xlb/precision_policy.py:57-97) */
+    int64_t q_stride;                  /* elements between populations of f fields */
+    int64_t mask_q_stride;             /* elements between directions of missing_mask */
+} XlbDomain;
+
+const char* xlb_last_error(void);
+int xlb_abi_version(void);
+int xlb_bc_entry_size(void);
+int xlb_domain_size(void);
+/* number of kernels this library has launched from the calling process (for bench gpu_launches) */
+long long xlb_launch_count(void);
+
+/* IncompressibleNavierStokesStepper.__call__  (nse_stepper.py:227-282 JAX pull; :427-476 Warp kernel)
+ * f1[:, x_begin:x_end] = collide(bc(stream(f0)))  -- one fused launch.  bc_table/bc_mask/missing_mask
+ * may be NULL when n_bc == 0 (fully periodic). */
+int xlb_step(const XlbDomain* dom, int collision, const void* f0, void* f1, const uint8_t* bc_mask,
+             const uint8_t* missing_mask, const XlbBcEntry* bc_table, int n_bc, double omega, int timestep,
+             int x_begin, int x_end, int variant, void* stream);
+
+/* Stream.__call__ (stream.py:29-62): f_out[l,x] = f_in[l, x - c_l] periodic. dtype = element type. */
+int xlb_stream(const XlbDomain* dom, int dtype, const void* f_in, void* f_out, void* stream);
+/* Macroscopic / ZeroMoment / FirstMoment (macroscopic.py:21-26, zero_moment.py:14-17, first_moment.py:14-18).
+ * rho [1,N] and/or u [d,N] may be NULL (then not written); first moment divides by the computed rho. */
+int xlb_macroscopic(const XlbDomain* dom, int f_dtype, const void* f, int out_dtype, void* rho, void* u, void* stream);
+/* SecondMoment (second_moment.py:35-55): pi [d(d+1)/2, N] */
+int xlb_second_moment(const XlbDomain* dom, int f_dtype, const void* f, int out_dtype, void* pi, void* stream);
+/* QuadraticEquilibrium (quadratic_equilibrium.py:23-30): f[q,N] from rho[1,N], u[d,N] */
+int xlb_equilibrium(const XlbDomain* dom, int in_dtype, const void* rho, const void* u, int f_dtype, void* f, void* stream);
+/* BGK / KBC (bgk.py:27-32, kbc.py:40-79): fout = collide(f, feq, omega); all three share dtype */
+int xlb_collide(const XlbDomain* dom, int collision, int dtype, const void* f, const void* feq, void* fout, double omega, void* stream);
+/* BoundaryCondition.__call__ (boundary_condition.py:146-180 Warp kernel; bc_*.py JAX): applies BC ``id`` of
+ * bc_table on cells with bc_mask == id, reading f_pre / f_post and writing f_out (may alias f_post).
+ * assemble != 0 runs ExtrapolationOutflowBC.assemble_auxiliary_data (bc_extrapolation_outflow.py:106-133) instead. */
+int xlb_apply_bc(const XlbDomain* dom, int dtype, const void* f_pre, const void* f_post, void* f_out, const uint8_t* bc_mask,
+                 const uint8_t* missing_mask, const XlbBcEntry* bc_table, int id, int assemble, void* stream);
+
+/* IndicesBoundaryMasker (indices_boundary_masker.py:73-143), split in two device passes:
+ * (1) tag: for every index column i (indices int32 [d][n], global coordinates minus ``origin``): cells outside
+ *     the local block are dropped; bc_mask[cell] = id when id >= 0; solid[cell] = 1 when mark_solid != 0.
+ *     Optional per-direction padding (pad != 0) tags index + c_l for all l (boundary_condition.py:123-136).
+ * (2) missing: missing[l, x] = 1 iff x - c_l is outside the *global* domain or solid (the streamed mask, :134). */
+int xlb_mask_tag(const XlbDomain* dom, const int32_t* indices, int64_t n, const int32_t origin[3], const int32_t global_shape[3], int id,
+                 int mark_solid, int pad, uint8_t* bc_mask, uint8_t* solid, void* stream);
+int xlb_mask_missing(const XlbDomain* dom, const uint8_t* solid, const int32_t origin[3], const int32_t global_shape[3],
+                     uint8_t* missing_mask, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* XLB_B200_H */

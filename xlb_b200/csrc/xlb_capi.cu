@@ -1,0 +1,289 @@
+// xlb_capi.cu -- extern "C" surface of libxlb_b200.so (declared in include/xlb_b200.h).
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+
+#include "xlb_host.cuh"
+#include "xlb_ops.cuh"
+
+namespace xlb {
+
+static thread_local char g_err[512] = "";
+static std::atomic<long long> g_launches{0};
+
+int set_error(int code, const char* msg) {
+    std::snprintf(g_err, sizeof(g_err), "%s", msg);
+    return code;
+}
+
+int count_launch(cudaError_t err) {
+    if (err != cudaSuccess) {
+        std::snprintf(g_err, sizeof(g_err), "CUDA error %d: %s", (int)err, cudaGetErrorString(err));
+        return (int)err;
+    }
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return 0;
+}
+
+static int check_domain(const XlbDomain* d, const char* who) {
+    if (!d) return set_error(XLB_EINVAL, "null XlbDomain");
+    const bool lat_ok = (d->d == 2 && d->q == 9) || (d->d == 3 && (d->q == 19 || d->q == 27));
+    if (!lat_ok) return set_error(XLB_EUNSUPPORTED, "unsupported velocity set (need D2Q9, D3Q19 or D3Q27)");
+    if (d->nx < 1 || d->ny < 1 || d->nz < 1) return set_error(XLB_EINVAL, "domain extents must be >= 1");
+    if (d->d == 2 && d->nx != 1) return set_error(XLB_EINVAL, "2-D fields are passed as nx=1, ny=NX, nz=NY");
+    (void)who;
+    return 0;
+}
+
+static OpParams make_op(const XlbDomain* d) {
+    OpParams p;
+    std::memset(&p, 0, sizeof(p));
+    p.nx = d->nx;
+    p.ny = d->ny;
+    p.nz = d->nz;
+    p.x_periodic = d->x_periodic;
+    p.ncell = (long long)d->nx * d->ny * d->nz;
+    p.qs = d->q_stride ? d->q_stride : p.ncell;
+    p.mqs = d->mask_q_stride ? d->mask_q_stride : p.ncell;
+    return p;
+}
+
+static unsigned blocks_for(long long n, int b) { return (unsigned)((n + b - 1) / b); }
+
+// dispatch helper: call F<T,Q>(...) for the runtime (compute dtype, q)
+#define XLB_DISPATCH_TQ(dom, CALL)                                                       \
+    do {                                                                                 \
+        const int q_ = (dom)->q;                                                         \
+        if ((dom)->compute_dtype == XLB_F64) {                                           \
+            using T = double;                                                            \
+            if (q_ == 9) { constexpr int Q = 9; CALL; }                                  \
+            else if (q_ == 19) { constexpr int Q = 19; CALL; }                           \
+            else { constexpr int Q = 27; CALL; }                                         \
+        } else {                                                                         \
+            using T = float;                                                             \
+            if (q_ == 9) { constexpr int Q = 9; CALL; }                                  \
+            else if (q_ == 19) { constexpr int Q = 19; CALL; }                           \
+            else { constexpr int Q = 27; CALL; }                                         \
+        }                                                                                \
+    } while (0)
+
+}  // namespace xlb
+
+using namespace xlb;
+
+extern "C" {
+
+const char* xlb_last_error(void) { return g_err; }
+int xlb_abi_version(void) { return XLB_B200_ABI_VERSION; }
+int xlb_bc_entry_size(void) { return (int)sizeof(XlbBcEntry); }
+int xlb_domain_size(void) { return (int)sizeof(XlbDomain); }
+long long xlb_launch_count(void) { return g_launches.load(); }
+
+int xlb_step(const XlbDomain* dom, int collision, const void* f0, void* f1, const uint8_t* bc_mask, const uint8_t* missing_mask,
+             const XlbBcEntry* bc_table, int n_bc, double omega, int timestep, int x_begin, int x_end, int variant, void* stream) {
+    (void)timestep;  // carried for signature parity with nse_stepper.py:229; the JAX path never reads it
+    if (int rc = check_domain(dom, "xlb_step")) return rc;
+    if (!f0 || !f1) return set_error(XLB_EINVAL, "xlb_step: null population pointer");
+    if (f0 == f1) return set_error(XLB_EINVAL, "xlb_step: f0 and f1 must be distinct buffers (pull scheme, double buffered)");
+    if (x_begin < 0 || x_end > dom->nx || x_begin > x_end) return set_error(XLB_EINVAL, "xlb_step: bad x range");
+    if (!dom->x_periodic && (x_begin < 1 || x_end > dom->nx - 1) && dom->d == 3)
+        return set_error(XLB_EINVAL, "xlb_step: non-periodic x needs ghost planes at x_begin-1 and x_end");
+    if (x_begin == x_end) return 0;
+    StepParams p;
+    std::memset(&p, 0, sizeof(p));
+    p.f0 = f0;
+    p.f1 = f1;
+    const bool has_bc = n_bc > 0 && bc_mask && bc_table;
+    if (n_bc > 0 && !has_bc) return set_error(XLB_EINVAL, "xlb_step: n_bc > 0 needs bc_mask and bc_table");
+    p.bc_mask = has_bc ? bc_mask : nullptr;
+    p.missing = has_bc ? missing_mask : nullptr;
+    p.bct = has_bc ? bc_table : nullptr;
+    p.nx = dom->nx;
+    p.ny = dom->ny;
+    p.nz = dom->nz;
+    p.x_begin = x_begin;
+    p.x_end = x_end;
+    p.x_periodic = dom->x_periodic;
+    const long long ncell = (long long)dom->nx * dom->ny * dom->nz;
+    p.qs = dom->q_stride ? dom->q_stride : ncell;
+    p.mqs = dom->mask_q_stride ? dom->mask_q_stride : ncell;
+    p.omega = omega;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int key = dom->q * 100 + dom->compute_dtype * 10 + dom->store_dtype;
+    switch (key) {
+#define XLB_CASE(Q, C, S, tag) \
+    case Q * 100 + C * 10 + S: return xlb_step_q##Q##_##tag(collision, p, variant, st);
+#define XLB_CASES(Q)                        \
+    XLB_CASE(Q, XLB_F32, XLB_F32, f32f32)   \
+    XLB_CASE(Q, XLB_F32, XLB_F16, f32f16)   \
+    XLB_CASE(Q, XLB_F64, XLB_F64, f64f64)   \
+    XLB_CASE(Q, XLB_F64, XLB_F32, f64f32)   \
+    XLB_CASE(Q, XLB_F64, XLB_F16, f64f16)
+        XLB_CASES(9)
+        XLB_CASES(19)
+        XLB_CASES(27)
+        default: return set_error(XLB_EUNSUPPORTED, "xlb_step: unsupported precision policy (precision_policy.py:57-97)");
+    }
+}
+
+int xlb_stream(const XlbDomain* dom, int dtype, const void* f_in, void* f_out, void* stream) {
+    if (int rc = check_domain(dom, "xlb_stream")) return rc;
+    if (!f_in || !f_out || f_in == f_out) return set_error(XLB_EINVAL, "xlb_stream: need two distinct buffers");
+    OpParams p = make_op(dom);
+    p.a = f_in;
+    p.o0 = f_out;
+    p.dt_in = p.dt_out = dtype;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const unsigned nb = blocks_for(p.ncell, 256);
+    if (dom->q == 9) stream_kernel<9><<<nb, 256, 0, st>>>(p);
+    else if (dom->q == 19) stream_kernel<19><<<nb, 256, 0, st>>>(p);
+    else stream_kernel<27><<<nb, 256, 0, st>>>(p);
+    return count_launch(cudaGetLastError());
+}
+
+int xlb_macroscopic(const XlbDomain* dom, int f_dtype, const void* f, int out_dtype, void* rho, void* u, void* stream) {
+    if (int rc = check_domain(dom, "xlb_macroscopic")) return rc;
+    if (!f) return set_error(XLB_EINVAL, "xlb_macroscopic: null f");
+    OpParams p = make_op(dom);
+    p.a = f;
+    p.o0 = rho;
+    p.o1 = u;
+    p.dt_in = f_dtype;
+    p.dt_out = out_dtype;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const unsigned nb = blocks_for(p.ncell, 256);
+    XLB_DISPATCH_TQ(dom, (macroscopic_kernel<T, Q><<<nb, 256, 0, st>>>(p)));
+    return count_launch(cudaGetLastError());
+}
+
+int xlb_second_moment(const XlbDomain* dom, int f_dtype, const void* f, int out_dtype, void* pi, void* stream) {
+    if (int rc = check_domain(dom, "xlb_second_moment")) return rc;
+    if (!f || !pi) return set_error(XLB_EINVAL, "xlb_second_moment: null pointer");
+    OpParams p = make_op(dom);
+    p.a = f;
+    p.o0 = pi;
+    p.dt_in = f_dtype;
+    p.dt_out = out_dtype;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const unsigned nb = blocks_for(p.ncell, 256);
+    XLB_DISPATCH_TQ(dom, (second_moment_kernel<T, Q><<<nb, 256, 0, st>>>(p)));
+    return count_launch(cudaGetLastError());
+}
+
+int xlb_equilibrium(const XlbDomain* dom, int in_dtype, const void* rho, const void* u, int f_dtype, void* f, void* stream) {
+    if (int rc = check_domain(dom, "xlb_equilibrium")) return rc;
+    if (!rho || !u || !f) return set_error(XLB_EINVAL, "xlb_equilibrium: null pointer");
+    OpParams p = make_op(dom);
+    p.a = rho;
+    p.b = u;
+    p.o0 = f;
+    p.dt_in = in_dtype;
+    p.dt_out = f_dtype;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const unsigned nb = blocks_for(p.ncell, 256);
+    XLB_DISPATCH_TQ(dom, (equilibrium_kernel<T, Q><<<nb, 256, 0, st>>>(p)));
+    return count_launch(cudaGetLastError());
+}
+
+int xlb_collide(const XlbDomain* dom, int collision, int dtype, const void* f, const void* feq, void* fout, double omega, void* stream) {
+    if (int rc = check_domain(dom, "xlb_collide")) return rc;
+    if (!f || !feq || !fout) return set_error(XLB_EINVAL, "xlb_collide: null pointer");
+    if (collision == XLB_KBC && dom->q == 19)
+        return set_error(XLB_EUNSUPPORTED, "KBC: velocity set not supported (needs D2Q9 or D3Q27; kbc.py:65-66)");
+    if (collision != XLB_BGK && collision != XLB_KBC) return set_error(XLB_EINVAL, "xlb_collide: unknown collision model");
+    OpParams p = make_op(dom);
+    p.a = f;
+    p.b = feq;
+    p.o0 = fout;
+    p.dt_in = p.dt_out = dtype;
+    p.omega = omega;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const unsigned nb = blocks_for(p.ncell, 128);
+    if (collision == XLB_BGK) {
+        XLB_DISPATCH_TQ(dom, (collide_kernel<T, Q, XLB_BGK><<<nb, 128, 0, st>>>(p)));
+    } else if (dom->q == 9) {
+        if (dom->compute_dtype == XLB_F64) collide_kernel<double, 9, XLB_KBC><<<nb, 128, 0, st>>>(p);
+        else collide_kernel<float, 9, XLB_KBC><<<nb, 128, 0, st>>>(p);
+    } else {
+        if (dom->compute_dtype == XLB_F64) collide_kernel<double, 27, XLB_KBC><<<nb, 128, 0, st>>>(p);
+        else collide_kernel<float, 27, XLB_KBC><<<nb, 128, 0, st>>>(p);
+    }
+    return count_launch(cudaGetLastError());
+}
+
+int xlb_apply_bc(const XlbDomain* dom, int dtype, const void* f_pre, const void* f_post, void* f_out, const uint8_t* bc_mask,
+                 const uint8_t* missing_mask, const XlbBcEntry* bc_table, int id, int assemble, void* stream) {
+    if (int rc = check_domain(dom, "xlb_apply_bc")) return rc;
+    if (!f_pre || !f_post || !f_out || !bc_mask || !missing_mask || !bc_table) return set_error(XLB_EINVAL, "xlb_apply_bc: null pointer");
+    if (id < 1 || id > 255) return set_error(XLB_EINVAL, "xlb_apply_bc: id must be in 1..255");
+    OpParams p = make_op(dom);
+    p.a = f_pre;
+    p.b = f_post;
+    p.o0 = f_out;
+    p.bc_mask = bc_mask;
+    p.missing = missing_mask;
+    p.bct = bc_table;
+    p.dt_in = p.dt_out = dtype;
+    p.id = id;
+    p.flag = assemble;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const unsigned nb = blocks_for(p.ncell, 128);
+    XLB_DISPATCH_TQ(dom, (apply_bc_kernel<T, Q><<<nb, 128, 0, st>>>(p)));
+    return count_launch(cudaGetLastError());
+}
+
+static MaskParams make_mask(const XlbDomain* d, const int32_t origin[3], const int32_t gshape[3]) {
+    MaskParams p;
+    std::memset(&p, 0, sizeof(p));
+    p.nx = d->nx;
+    p.ny = d->ny;
+    p.nz = d->nz;
+    for (int a = 0; a < 3; ++a) {
+        p.origin[a] = origin ? origin[a] : 0;
+        p.gshape[a] = gshape ? gshape[a] : (a == 0 ? d->nx : (a == 1 ? d->ny : d->nz));
+    }
+    const long long ncell = (long long)d->nx * d->ny * d->nz;
+    p.mqs = d->mask_q_stride ? d->mask_q_stride : ncell;
+    return p;
+}
+
+int xlb_mask_tag(const XlbDomain* dom, const int32_t* indices, int64_t n, const int32_t origin[3], const int32_t global_shape[3], int id,
+                   int mark_solid, int pad, uint8_t* bc_mask, uint8_t* solid, void* stream) {
+    if (int rc = check_domain(dom, "xlb_mask_tag")) return rc;
+    if (n == 0) return 0;
+    if (!indices) return set_error(XLB_EINVAL, "xlb_mask_tag: null indices");
+    if (id > 255) return set_error(XLB_EINVAL, "xlb_mask_tag: id must fit a uint8");
+    MaskParams p = make_mask(dom, origin, global_shape);
+    p.idx = indices;
+    p.n = n;
+    p.id = id;
+    p.mark_solid = mark_solid;
+    p.pad = pad;
+    p.bc_mask = bc_mask;
+    p.solid = solid;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const long long total = pad ? n * dom->q : n;
+    const unsigned nb = blocks_for(total, 256);
+    if (dom->q == 9) mask_tag_kernel<9><<<nb, 256, 0, st>>>(p);
+    else if (dom->q == 19) mask_tag_kernel<19><<<nb, 256, 0, st>>>(p);
+    else mask_tag_kernel<27><<<nb, 256, 0, st>>>(p);
+    return count_launch(cudaGetLastError());
+}
+
+int xlb_mask_missing(const XlbDomain* dom, const uint8_t* solid, const int32_t origin[3], const int32_t global_shape[3],
+                     uint8_t* missing_mask, void* stream) {
+    if (int rc = check_domain(dom, "xlb_mask_missing")) return rc;
+    if (!missing_mask) return set_error(XLB_EINVAL, "xlb_mask_missing: null missing_mask");
+    MaskParams p = make_mask(dom, origin, global_shape);
+    p.solid_in = solid;
+    p.missing = missing_mask;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const long long ncell = (long long)dom->nx * dom->ny * dom->nz;
+    const unsigned nb = blocks_for(ncell, 256);
+    if (dom->q == 9) mask_missing_kernel<9><<<nb, 256, 0, st>>>(p);
+    else if (dom->q == 19) mask_missing_kernel<19><<<nb, 256, 0, st>>>(p);
+    else mask_missing_kernel<27><<<nb, 256, 0, st>>>(p);
+    return count_launch(cudaGetLastError());
+}
+
+}  // extern "C"

@@ -1,0 +1,182 @@
+// xlb_common.cuh -- lattice traits, typed vector access and shared parameter blocks.
+//
+// Lattice direction order is the reference's (xlb/velocity_set/d3q19.py:17-30, d3q27.py:17-32,
+// d2q9.py:16-24): itertools.product([0,-1,1], repeat=3), x slowest; D3Q19 keeps |c|_1 <= 2.
+// All tables are constexpr functions so that fully unrolled loops fold them into immediates.
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <type_traits>
+#include <utility>
+
+#include "../../include/xlb_b200.h"
+
+#define XLB_HD __host__ __device__ __forceinline__
+#define XLB_D __device__ __forceinline__
+
+namespace xlb {
+
+// ----------------------------------------------------------------------------- lattices
+// Kernel axes are always 3-D (x slowest, z fastest).  D2Q9 fields [q][NX][NY] run as
+// nx=1, ny=NX, nz=NY, i.e. user axis a maps to kernel axis a+1.
+template <int Q>
+struct Lat;
+
+XLB_HD constexpr int digit3(int v) { return v == 0 ? 0 : (v == 1 ? -1 : 1); }
+
+template <>
+struct Lat<27> {
+    static constexpr int Q = 27, D = 3;
+    XLB_HD static constexpr int c(int l, int a) { return a == 0 ? digit3(l / 9) : (a == 1 ? digit3((l / 3) % 3) : digit3(l % 3)); }
+    XLB_HD static constexpr double w(int l) {
+        int n = (c(l, 0) != 0) + (c(l, 1) != 0) + (c(l, 2) != 0);
+        return n == 0 ? 8.0 / 27.0 : (n == 1 ? 2.0 / 27.0 : (n == 2 ? 1.0 / 54.0 : 1.0 / 216.0));
+    }
+};
+
+template <>
+struct Lat<19> {
+    static constexpr int Q = 19, D = 3;
+    // index of the l-th member of the D3Q27 enumeration with |c|_1 <= 2
+    XLB_HD static constexpr int l27(int l) {
+        int k = 0;
+        for (int m = 0; m < 27; ++m) {
+            int n = (Lat<27>::c(m, 0) != 0) + (Lat<27>::c(m, 1) != 0) + (Lat<27>::c(m, 2) != 0);
+            if (n <= 2) {
+                if (k == l) return m;
+                ++k;
+            }
+        }
+        return 0;
+    }
+    XLB_HD static constexpr int c(int l, int a) { return Lat<27>::c(l27(l), a); }
+    XLB_HD static constexpr double w(int l) {
+        int n = (c(l, 0) != 0) + (c(l, 1) != 0) + (c(l, 2) != 0);
+        return n == 0 ? 1.0 / 3.0 : (n == 1 ? 1.0 / 18.0 : 1.0 / 36.0);
+    }
+};
+
+template <>
+struct Lat<9> {
+    static constexpr int Q = 9, D = 2;
+    XLB_HD static constexpr int cx2(int l) {
+        constexpr int t[9] = {0, 0, 0, 1, -1, 1, -1, 1, -1};
+        return t[l];
+    }
+    XLB_HD static constexpr int cy2(int l) {
+        constexpr int t[9] = {0, 1, -1, 0, 1, -1, 0, 1, -1};
+        return t[l];
+    }
+    XLB_HD static constexpr int c(int l, int a) { return a == 0 ? 0 : (a == 1 ? cx2(l) : cy2(l)); }
+    XLB_HD static constexpr double w(int l) {
+        int n = (cx2(l) != 0) + (cy2(l) != 0);
+        return n == 0 ? 4.0 / 9.0 : (n == 1 ? 1.0 / 9.0 : 1.0 / 36.0);
+    }
+};
+
+template <int Q>
+XLB_HD constexpr int opp(int l) {  // velocity_set.py:182-196
+    for (int m = 0; m < Q; ++m)
+        if (Lat<Q>::c(m, 0) == -Lat<Q>::c(l, 0) && Lat<Q>::c(m, 1) == -Lat<Q>::c(l, 1) && Lat<Q>::c(m, 2) == -Lat<Q>::c(l, 2)) return m;
+    return 0;
+}
+template <int Q>
+XLB_HD constexpr bool is_main(int l) {  // velocity_set.py:198-212
+    return (Lat<Q>::c(l, 0) != 0) + (Lat<Q>::c(l, 1) != 0) + (Lat<Q>::c(l, 2) != 0) == 1;
+}
+// first kernel axis that carries a lattice dimension (1 for D2Q9, 0 otherwise)
+template <int Q>
+XLB_HD constexpr int axis0() { return 3 - Lat<Q>::D; }
+
+// Compile-time loop: f(std::integral_constant<int, I>) for I in [0, N).  Every lattice-table lookup
+// inside the body is then a true constant expression (folded by the front end, not by unrolling).
+template <typename F, int... Is>
+XLB_D void static_for_impl(F&& f, std::integer_sequence<int, Is...>) {
+    (f(std::integral_constant<int, Is>{}), ...);
+}
+template <int N, typename F>
+XLB_D void static_for(F&& f) {
+    static_for_impl(static_cast<F&&>(f), std::make_integer_sequence<int, N>{});
+}
+#define XLB_IDX(name, tag) constexpr int name = decltype(tag)::value
+
+// ----------------------------------------------------------------------------- element access
+template <typename S>
+struct DtypeOf;
+template <>
+struct DtypeOf<__half> { static constexpr int value = XLB_F16; };
+template <>
+struct DtypeOf<float> { static constexpr int value = XLB_F32; };
+template <>
+struct DtypeOf<double> { static constexpr int value = XLB_F64; };
+
+template <typename T, typename S>
+XLB_D T to_compute(S v) { return static_cast<T>(v); }
+template <>
+XLB_D float to_compute<float, __half>(__half v) { return __half2float(v); }
+template <>
+XLB_D double to_compute<double, __half>(__half v) { return static_cast<double>(__half2float(v)); }
+
+template <typename S, typename T>
+XLB_D S to_store(T v) { return static_cast<S>(v); }  // cvt.rn (round-to-nearest-even), precision_policy.py:105-110
+template <>
+XLB_D __half to_store<__half, float>(float v) { return __float2half_rn(v); }
+template <>
+XLB_D __half to_store<__half, double>(double v) { return __double2half(v); }
+
+// V consecutive elements, naturally aligned so that one LDG/STG moves all of them (<= 16 B)
+template <typename S, int V>
+struct alignas(sizeof(S) * V) Vec {
+    S v[V];
+};
+
+template <typename S, int V>
+XLB_D Vec<S, V> ld_vec(const S* p) { return *reinterpret_cast<const Vec<S, V>*>(p); }
+template <typename S, int V>
+XLB_D void st_vec(S* p, const Vec<S, V>& x) { *reinterpret_cast<Vec<S, V>*>(p) = x; }
+
+XLB_D float shfl_up1(float v) { return __shfl_up_sync(0xffffffffu, v, 1); }
+XLB_D double shfl_up1(double v) { return __shfl_up_sync(0xffffffffu, v, 1); }
+XLB_D __half shfl_up1(__half v) { return __shfl_up_sync(0xffffffffu, v, 1); }
+XLB_D float shfl_down1(float v) { return __shfl_down_sync(0xffffffffu, v, 1); }
+XLB_D double shfl_down1(double v) { return __shfl_down_sync(0xffffffffu, v, 1); }
+XLB_D __half shfl_down1(__half v) { return __shfl_down_sync(0xffffffffu, v, 1); }
+
+// runtime-typed scalar access for the stand-alone operators and BC side data
+template <typename T>
+XLB_D T ld_any(const void* p, int dtype, int64_t i) {
+    if (dtype == XLB_F32) return static_cast<T>(static_cast<const float*>(p)[i]);
+    if (dtype == XLB_F64) return static_cast<T>(static_cast<const double*>(p)[i]);
+    return static_cast<T>(__half2float(static_cast<const __half*>(p)[i]));
+}
+template <typename T>
+XLB_D void st_any(void* p, int dtype, int64_t i, T v) {
+    if (dtype == XLB_F32)
+        static_cast<float*>(p)[i] = static_cast<float>(v);
+    else if (dtype == XLB_F64)
+        static_cast<double*>(p)[i] = static_cast<double>(v);
+    else
+        static_cast<__half*>(p)[i] = to_store<__half, T>(v);
+}
+
+// ----------------------------------------------------------------------------- kernel parameter block
+struct StepParams {
+    const void* f0;
+    void* f1;
+    const uint8_t* bc_mask;
+    const uint8_t* missing;
+    const XlbBcEntry* bct;
+    int nx, ny, nz;
+    int x_begin, x_end;
+    int x_periodic;
+    int ntz;  // nz / V
+    long long qs;   // population stride (elements)
+    long long mqs;  // missing-mask direction stride
+    double omega;
+};
+
+XLB_HD bool bc_is_complex(int kind) { return kind >= XLB_BC_HALFWAY; }
+
+}  // namespace xlb

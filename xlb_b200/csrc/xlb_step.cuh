@@ -1,0 +1,222 @@
+// xlb_step.cuh -- the fused per-timestep kernel (K1) and its generic per-cell engine.
+//
+// Replaces IncompressibleNavierStokesStepper.__call__ (xlb/operator/stepper/nse_stepper.py:
+// 238-282 JAX pull path = semantics; :427-464 Warp kernel = GPU design reference).
+//
+// Layout: SoA populations f[l][x][y][z], z fastest.  One thread owns V consecutive z cells
+// (V * sizeof(store type) <= 16 B), so every population is moved with one aligned vector
+// LDG/STG per thread; the +-1 z shift of the pull is resolved with a warp shuffle of the
+// single edge element (edge lanes of a row fall back to one scalar load).  Populations stay
+// in registers from load to store; boundary handling is keyed on the packed bc_mask bytes:
+//   * bc == 0 for all V cells        -> branch-free fast path
+//   * FullwayBounceBack/EquilibriumBC -> in-register selects (no extra memory traffic)
+//   * every other BC kind             -> cell_update_generic() below, per cell.
+#pragma once
+#include "xlb_math.cuh"
+
+namespace xlb {
+
+XLB_D int wrap1(int v, int n) { return v < 0 ? v + n : (v >= n ? v - n : v); }
+XLB_D int wrapn(int v, int n) {
+    v %= n;
+    return v < 0 ? v + n : v;
+}
+
+// ------------------------------------------------------------------ generic per-cell engine
+// Handles every BC kind; all reads come from f0, the only write is the cell's own f1 column.
+template <typename T, typename S, int Q, int COLL>
+__device__ __noinline__ void cell_update_generic(const StepParams& p, int x, int y, int z) {
+    const S* __restrict__ f0 = static_cast<const S*>(p.f0);
+    S* __restrict__ f1 = static_cast<S*>(p.f1);
+    const long long cell = ((long long)x * p.ny + y) * p.nz + z;
+    const int id = p.bc_mask ? p.bc_mask[cell] : 0;
+    int kind = XLB_BC_NONE;
+    const XlbBcEntry* e = nullptr;
+    if (id != 0) {
+        e = p.bct + id;
+        kind = e->kind;
+    }
+    T f[Q][1];
+    // pull-stream (stream.py:29-62)
+    static_for<Q>([&](auto lc) {
+        XLB_IDX(l, lc);
+        using D = Dir<Q, l>;
+        int xs = x - D::cx;
+        if (p.x_periodic) xs = wrap1(xs, p.nx);
+        const int ys = wrap1(y - D::cy, p.ny);
+        const int zs = wrap1(z - D::cz, p.nz);
+        f[l][0] = to_compute<T, S>(f0[l * p.qs + ((long long)xs * p.ny + ys) * p.nz + zs]);
+    });
+    uint32_t miss = 0;
+    if (kind >= XLB_BC_HALFWAY && kind != XLB_BC_DONOTHING) {
+#pragma unroll
+        for (int l = 0; l < Q; ++l) miss |= (p.missing[l * p.mqs + cell] ? 1u : 0u) << l;
+    }
+    // ---- STREAMING-step boundary conditions (nse_stepper.py:250-257)
+    if (kind == XLB_BC_EQUILIBRIUM) {
+#pragma unroll
+        for (int l = 0; l < Q; ++l) f[l][0] = static_cast<T>(e->table[l]);
+    } else if (kind == XLB_BC_DONOTHING) {
+#pragma unroll
+        for (int l = 0; l < Q; ++l) f[l][0] = to_compute<T, S>(f0[l * p.qs + cell]);
+    } else if (kind == XLB_BC_HALFWAY || kind == XLB_BC_EXTRAPOLATION) {
+        // f_post[l] = f_pre[opp l] (+ 6 w_l c_l.u_wall) where missing[l]
+        static_for<Q>([&](auto lc) {
+            XLB_IDX(l, lc);
+            if (miss & (1u << l)) {
+                T v = to_compute<T, S>(f0[Dir<Q, l>::o * p.qs + cell]);
+                if (kind == XLB_BC_HALFWAY) v = v + static_cast<T>(e->table[l]);
+                f[l][0] = v;
+            }
+        });
+    } else if (kind == XLB_BC_ZOUHE_VELOCITY || kind == XLB_BC_ZOUHE_PRESSURE) {
+        zouhe_apply<T, Q>(f, miss, *e, kind == XLB_BC_ZOUHE_VELOCITY, x, y, z);
+    }
+    // ---- macroscopic, equilibrium, collision (+ COLLISION-step FullwayBounceBackBC)
+    T fps[Q];
+    if (kind == XLB_BC_EXTRAPOLATION) {
+#pragma unroll
+        for (int l = 0; l < Q; ++l) fps[l] = f[l][0];
+    }
+    collide_column<T, Q, COLL, 1, 0>(f, static_cast<T>(p.omega), kind == XLB_BC_FULLWAY);
+    // ---- ExtrapolationOutflowBC.assemble_auxiliary_data (bc_extrapolation_outflow.py:106-133)
+    if (kind == XLB_BC_EXTRAPOLATION) {
+        const T cs = T(1.0) / sqrt(T(3.0));
+        const int xn = x - e->normal[0], yn = y - e->normal[1], zn = z - e->normal[2];
+        static_for<Q>([&](auto lc) {
+            XLB_IDX(l, lc);
+            using D = Dir<Q, l>;
+            if (miss & (1u << l)) {
+                int xs = xn - D::cx;
+                if (p.x_periodic) xs = wrapn(xs, p.nx);
+                const int ys = wrapn(yn - D::cy, p.ny);
+                const int zs = wrapn(zn - D::cz, p.nz);
+                const T nb = to_compute<T, S>(f0[l * p.qs + ((long long)xs * p.ny + ys) * p.nz + zs]);
+                f[D::o][0] = cs * nb + (T(1.0) - cs) * fps[l];
+            }
+        });
+    }
+#pragma unroll
+    for (int l = 0; l < Q; ++l) f1[l * p.qs + cell] = to_store<S, T>(f[l][0]);
+}
+
+// every cell through the generic engine (variant XLB_VARIANT_GENERIC; cross-check + odd shapes)
+template <typename T, typename S, int Q, int COLL>
+__global__ void __launch_bounds__(128) step_generic_kernel(const __grid_constant__ StepParams p) {
+    const long long row = (long long)p.ny * p.nz;
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= row) return;
+    const int x = p.x_begin + blockIdx.y;
+    cell_update_generic<T, S, Q, COLL>(p, x, (int)(i / p.nz), (int)(i % p.nz));
+}
+
+// ------------------------------------------------------------------ fused vector kernel (K1)
+template <typename T, typename S, int Q, int COLL, int V, int BLOCK, int MINB, bool HAS_BC>
+__global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_constant__ StepParams p) {
+    const S* __restrict__ f0 = static_cast<const S*>(p.f0);
+    S* __restrict__ f1 = static_cast<S*>(p.f1);
+    const int nvec = p.ny * p.ntz;  // vectors per x plane
+    int i = blockIdx.x * BLOCK + threadIdx.x;
+    const bool active = i < nvec;
+    if (!active) i = nvec - 1;  // keep the lane alive for the shuffles
+    const int x = p.x_begin + blockIdx.y;
+    const int y = i / p.ntz;
+    const int tz = i - y * p.ntz;
+    const int z0 = tz * V;
+    const int lane = threadIdx.x & 31;
+    const long long cell = ((long long)x * p.ny + y) * p.nz + z0;
+
+    // ---- packed bc ids of my V cells
+    uint8_t ids[V];
+    bool any_bc = false, slow = false;
+    bool k_full[V], k_eq[V];
+#pragma unroll
+    for (int j = 0; j < V; ++j) k_full[j] = k_eq[j] = false;
+    if (HAS_BC) {
+        const Vec<uint8_t, V> w = ld_vec<uint8_t, V>(p.bc_mask + cell);
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+            ids[j] = w.v[j];
+            any_bc |= ids[j] != 0;
+        }
+        if (any_bc) {
+#pragma unroll
+            for (int j = 0; j < V; ++j) {
+                if (ids[j]) {
+                    const int k = p.bct[ids[j]].kind;
+                    k_full[j] = k == XLB_BC_FULLWAY;
+                    k_eq[j] = k == XLB_BC_EQUILIBRIUM;
+                    slow |= bc_is_complex(k);
+                }
+            }
+        }
+    }
+
+    // ---- pull-stream: one aligned vector load per population
+    const int xm = p.x_periodic ? wrap1(x - 1, p.nx) : x - 1;
+    const int xp = p.x_periodic ? wrap1(x + 1, p.nx) : x + 1;
+    const int ym = wrap1(y - 1, p.ny), yp = wrap1(y + 1, p.ny);
+    const bool edge_lo = (lane == 0) || (tz == 0);
+    const bool edge_hi = (lane == 31) || (tz == p.ntz - 1);
+    const int z_lo = (tz == 0) ? p.nz - 1 : z0 - 1;        // source of the element left of my vector
+    const int z_hi = (tz == p.ntz - 1) ? 0 : z0 + V;       // source of the element right of my vector
+    T f[Q][V];
+    static_for<Q>([&](auto lc) {
+        XLB_IDX(l, lc);
+        using D = Dir<Q, l>;
+        const int xs = D::cx == 0 ? x : (D::cx == 1 ? xm : xp);
+        const int ys = D::cy == 0 ? y : (D::cy == 1 ? ym : yp);
+        const S* row = f0 + l * p.qs + ((long long)xs * p.ny + ys) * p.nz;
+        const Vec<S, V> v = ld_vec<S, V>(row + z0);
+        if (D::cz == 0) {
+#pragma unroll
+            for (int j = 0; j < V; ++j) f[l][j] = to_compute<T, S>(v.v[j]);
+        } else if (D::cz == 1) {  // pull from z-1
+            S left = shfl_up1(v.v[V - 1]);
+            if (edge_lo) left = row[z_lo];
+            f[l][0] = to_compute<T, S>(left);
+#pragma unroll
+            for (int j = 1; j < V; ++j) f[l][j] = to_compute<T, S>(v.v[j - 1]);
+        } else {  // pull from z+1
+            S right = shfl_down1(v.v[0]);
+            if (edge_hi) right = row[z_hi];
+#pragma unroll
+            for (int j = 0; j < V - 1; ++j) f[l][j] = to_compute<T, S>(v.v[j + 1]);
+            f[l][V - 1] = to_compute<T, S>(right);
+        }
+    });
+    if (!active) return;
+
+    if (HAS_BC && slow) {
+        // a BC kind that needs f_pre / missing_mask / neighbour gathers: per-cell generic engine
+        for (int j = 0; j < V; ++j) cell_update_generic<T, S, Q, COLL>(p, x, y, z0 + j);
+        return;
+    }
+    if (HAS_BC && any_bc) {
+        // EquilibriumBC (STREAMING step): f_post_stream = feq(rho_bc, u_bc) constants
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+            if (k_eq[j]) {
+                const double* tab = p.bct[ids[j]].table;
+#pragma unroll
+                for (int l = 0; l < Q; ++l) f[l][j] = static_cast<T>(tab[l]);
+            }
+        }
+    }
+    const T omega = static_cast<T>(p.omega);
+    // ---- collide each of my cells in place
+    static_for<V>([&](auto jc) {
+        XLB_IDX(j, jc);
+        collide_column<T, Q, COLL, V, j>(f, omega, HAS_BC && k_full[j]);
+    });
+    // ---- one aligned vector store per population
+#pragma unroll
+    for (int l = 0; l < Q; ++l) {
+        Vec<S, V> o;
+#pragma unroll
+        for (int j = 0; j < V; ++j) o.v[j] = to_store<S, T>(f[l][j]);
+        st_vec<S, V>(f1 + l * p.qs + cell, o);
+    }
+}
+
+}  // namespace xlb

@@ -1,0 +1,76 @@
+// xlb_step_inst.cu -- one translation unit per (lattice, precision policy); compiled many times by
+// build.py with -DXLB_Q=<9|19|27> -DXLB_TC=<compute type> -DXLB_TS=<store type> -DXLB_TAG=<suffix>.
+// Exposes   int xlb_step_<tag>(const XlbDomain*, int collision, StepParams, int variant, cudaStream_t)
+#include "xlb_host.cuh"
+#include "xlb_step.cuh"
+
+#ifndef XLB_Q
+#error "compile with -DXLB_Q -DXLB_TC -DXLB_TS -DXLB_TAG"
+#endif
+
+// tuning knobs (overridable from the command line for sweeps; see tools/sweep.py)
+#ifndef XLB_TUNE_BLOCK
+#define XLB_TUNE_BLOCK 128
+#endif
+#ifndef XLB_TUNE_MINB
+#define XLB_TUNE_MINB 1
+#endif
+
+namespace xlb {
+
+template <typename T, typename S, int Q, int COLL, int V, bool HAS_BC>
+static int launch_vector(const StepParams& p0, cudaStream_t st) {
+    constexpr int BLOCK = XLB_TUNE_BLOCK;
+    StepParams p = p0;
+    p.ntz = p.nz / V;
+    const long long nvec = (long long)p.ny * p.ntz;
+    dim3 grid((unsigned)((nvec + BLOCK - 1) / BLOCK), (unsigned)(p.x_end - p.x_begin), 1);
+    step_vector_kernel<T, S, Q, COLL, V, BLOCK, XLB_TUNE_MINB, HAS_BC><<<grid, BLOCK, 0, st>>>(p);
+    return count_launch(cudaGetLastError());
+}
+
+template <typename T, typename S, int Q, int COLL>
+static int launch_generic(const StepParams& p, cudaStream_t st) {
+    const long long row = (long long)p.ny * p.nz;
+    dim3 grid((unsigned)((row + 127) / 128), (unsigned)(p.x_end - p.x_begin), 1);
+    step_generic_kernel<T, S, Q, COLL><<<grid, 128, 0, st>>>(p);
+    return count_launch(cudaGetLastError());
+}
+
+template <typename T, typename S, int Q, int COLL>
+static int step_coll(const StepParams& p, int variant, cudaStream_t st) {
+#ifdef XLB_TUNE_V
+    constexpr int VMAX = XLB_TUNE_V;
+#else
+    constexpr int VMAX = (sizeof(S) == 8) ? 2 : 4;
+#endif
+    const bool has_bc = p.bc_mask != nullptr && p.bct != nullptr;
+    if (variant == XLB_VARIANT_GENERIC) return launch_generic<T, S, Q, COLL>(p, st);
+    const uintptr_t a0 = reinterpret_cast<uintptr_t>(p.f0), a1 = reinterpret_cast<uintptr_t>(p.f1);
+    const bool vec_ok = (p.nz % VMAX == 0) && (p.qs % VMAX == 0) && (a0 % (VMAX * sizeof(S)) == 0) && (a1 % (VMAX * sizeof(S)) == 0) &&
+                        (!has_bc || reinterpret_cast<uintptr_t>(p.bc_mask) % VMAX == 0);
+    if (variant == XLB_VARIANT_VECTOR && !vec_ok) return set_error(XLB_EALIGN, "xlb_step: vector variant needs nz, q_stride and base pointers aligned to the vector width");
+    if (vec_ok && variant != XLB_VARIANT_SCALAR) {
+        return has_bc ? launch_vector<T, S, Q, COLL, VMAX, true>(p, st) : launch_vector<T, S, Q, COLL, VMAX, false>(p, st);
+    }
+    return has_bc ? launch_vector<T, S, Q, COLL, 1, true>(p, st) : launch_vector<T, S, Q, COLL, 1, false>(p, st);
+}
+
+}  // namespace xlb
+
+#define XLB_CAT2(a, b) a##b
+#define XLB_CAT(a, b) XLB_CAT2(a, b)
+
+int XLB_CAT(xlb_step_, XLB_TAG)(int collision, const xlb::StepParams& p, int variant, cudaStream_t st) {
+    using namespace xlb;
+#ifdef XLB_STUB  // tuning builds compile only the instance under test
+    (void)collision; (void)p; (void)variant; (void)st;
+    return set_error(XLB_EUNSUPPORTED, "xlb_step: this (lattice, policy) instance was stubbed out of a tuning build");
+#else
+    if (collision == XLB_BGK) return step_coll<XLB_TC, XLB_TS, XLB_Q, XLB_BGK>(p, variant, st);
+#if XLB_Q != 19
+    if (collision == XLB_KBC) return step_coll<XLB_TC, XLB_TS, XLB_Q, XLB_KBC>(p, variant, st);
+#endif
+    return set_error(XLB_EUNSUPPORTED, "xlb_step: collision model not supported for this velocity set (KBC needs D2Q9 or D3Q27; kbc.py:65-66)");
+#endif
+}

@@ -1,0 +1,55 @@
+"""Grid abstraction (xlb/grid/grid.py:19-58, 102-191)."""
+
+import numpy as np
+
+from ..default_config import DefaultConfig
+from ..compute_backend import ComputeBackend, require_cuda_backend
+
+
+def grid_factory(shape, compute_backend=None, velocity_set=None, backend_config=None):
+    """Same call as the reference; only ``ComputeBackend.CUDA`` exists here."""
+    compute_backend = compute_backend or DefaultConfig.default_backend
+    require_cuda_backend(compute_backend)
+    from .cuda_grid import CudaGrid
+
+    return CudaGrid(shape, backend_config=backend_config)
+
+
+class Grid:
+    def __init__(self, shape, compute_backend):
+        self.shape = tuple(int(s) for s in shape)
+        self.dim = len(self.shape)
+        self.compute_backend = compute_backend
+        self._initialize_backend()
+
+    def _initialize_backend(self):
+        raise NotImplementedError
+
+    def get_compute_backend(self):
+        return self.compute_backend
+
+    def bounding_box_indices(self, shape=None, remove_edges=False):
+        """Index lists of the domain faces (grid.py:135-191): 'left'/'right' = x min/max, 'front'/'back' =
+        y min/max (3-D), 'bottom'/'top' = last axis min/max.  ``remove_edges`` drops the rim of every face."""
+        shape = tuple(self.shape if shape is None else shape)
+        dim = len(shape)
+        lo = 1 if remove_edges else 0
+        rng = [np.arange(lo, n - lo) for n in shape]
+
+        def face(axis, value):
+            axes = [np.array([value]) if a == axis else rng[a] for a in range(dim)]
+            mesh = np.meshgrid(*axes, indexing="ij")
+            return [m.reshape(-1).tolist() for m in mesh]
+
+        if dim == 2:
+            nx, ny = shape
+            return {"bottom": face(1, 0), "top": face(1, ny - 1), "left": face(0, 0), "right": face(0, nx - 1)}
+        nx, ny, nz = shape
+        return {
+            "bottom": face(2, 0),
+            "top": face(2, nz - 1),
+            "left": face(0, 0),
+            "right": face(0, nx - 1),
+            "front": face(1, 0),
+            "back": face(1, ny - 1),
+        }

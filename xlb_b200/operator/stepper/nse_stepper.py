@@ -1,0 +1,136 @@
+"""Single-resolution incompressible Navier-Stokes stepper on the fused sm_100a kernel.
+
+Mirrors ``IncompressibleNavierStokesStepper`` of the reference (xlb/operator/stepper/nse_stepper.py:41-282):
+same constructor, ``prepare_fields(initializer=None) -> (f_0, f_1, bc_mask, missing_mask)`` and
+``stepper(f_0, f_1, bc_mask, missing_mask, omega, timestep) -> (f_0, f_1)`` with the result in ``f_1`` and the
+buffer swap left to the caller (examples/performance/mlups_3d.py:227-229).  One call = one launch of
+``xlb_step`` on the current torch CUDA stream; there is no host synchronisation inside.
+"""
+
+import numpy as np
+import torch
+
+from ... import _lib
+from ...compute_backend import ComputeBackend
+from ...default_config import DefaultConfig, current_device
+from ...helper.check_boundary_overlaps import check_bc_overlaps
+from ...helper.nse_fields import create_nse_fields
+from ..boundary_condition.boundary_condition import ImplementationStep
+from ..boundary_masker import IndicesBoundaryMasker
+from ..collision import BGK, KBC
+from ..equilibrium import QuadraticEquilibrium
+from ..macroscopic import Macroscopic
+from ..operator import Operator, byref, check, lib, stream_ptr
+from ..stream import Stream
+from .stepper import Stepper
+
+
+class IncompressibleNavierStokesStepper(Stepper):
+    def __init__(
+        self,
+        grid,
+        boundary_conditions=[],
+        collision_type="BGK",
+        streaming_scheme="pull",
+        forcing_scheme="exact_difference",
+        force_vector=None,
+        backend_config={},
+    ):
+        super().__init__(grid, boundary_conditions)
+        self.backend_config = backend_config
+        if collision_type == "BGK":
+            self.collision = BGK(self.velocity_set, self.precision_policy, self.compute_backend)
+        elif collision_type == "KBC":
+            self.collision = KBC(self.velocity_set, self.precision_policy, self.compute_backend)
+        else:
+            raise NotImplementedError(f"collision_type={collision_type!r} is outside the scope of the CUDA backend (BGK and KBC are implemented)")
+        if force_vector is not None:
+            raise NotImplementedError("forcing (ForcedCollision / ExactDifference) is outside the scope of the CUDA backend")
+        self.streaming_scheme = streaming_scheme
+        if streaming_scheme != "pull":
+            raise NotImplementedError(f"Unknown or unimplemented streaming scheme for backend: {self.compute_backend}")  # nse_stepper.py:91-92
+        self.stream = Stream(self.velocity_set, self.precision_policy, self.compute_backend)
+        self.equilibrium = QuadraticEquilibrium(self.velocity_set, self.precision_policy, self.compute_backend)
+        self.macroscopic = Macroscopic(self.velocity_set, self.precision_policy, self.compute_backend)
+        self.kernel_variant = int(self.backend_config.get("kernel_variant", _lib.VARIANT_AUTO)) if self.backend_config else _lib.VARIANT_AUTO
+        self._plan = None  # (key, domain struct, bc table tensor, n_bc)
+
+    # ------------------------------------------------------------------ setup (nse_stepper.py:99-205)
+    def prepare_fields(self, initializer=None):
+        _, f_0, f_1, missing_mask, bc_mask = create_nse_fields(
+            grid=self.grid, velocity_set=self.velocity_set, compute_backend=self.compute_backend, precision_policy=self.precision_policy
+        )
+        bc_mask, missing_mask = self._process_boundary_conditions(self.boundary_conditions, bc_mask, missing_mask)
+        if initializer is not None:
+            f_0 = initializer(bc_mask, f_0)
+        else:
+            from ...helper.initializers import initialize_eq
+
+            if f_0.numel() >= (1 << 28):
+                # rho = 1, u = 0 gives feq_l = w_l exactly; skip the rho/u temporaries on very large grids
+                w = self.velocity_set.w.astype(self.precision_policy.compute_precision.np_dtype)
+                for l in range(self.velocity_set.q):
+                    f_0[l].fill_(float(w[l]))
+            else:
+                f_0 = initialize_eq(f_0, self.grid, self.velocity_set, self.precision_policy, self.compute_backend)
+        return f_0, f_1, bc_mask, missing_mask
+
+    def _process_boundary_conditions(self, boundary_conditions, bc_mask, missing_mask):
+        check_bc_overlaps(boundary_conditions, self.velocity_set.d, self.compute_backend)
+        with_indices = [bc for bc in boundary_conditions if getattr(bc, "indices", None) is not None]
+        if with_indices:
+            masker = IndicesBoundaryMasker(
+                velocity_set=self.velocity_set, precision_policy=self.precision_policy, compute_backend=self.compute_backend, grid=self.grid
+            )
+            start = None
+            gshape = None
+            if getattr(self.grid, "halo", 0) or getattr(self.grid, "x_offset", 0):
+                start = (self.grid.x_offset - self.grid.halo,) + (0,) * (self.velocity_set.d - 1)
+                gshape = self.grid.global_shape
+            bc_mask, missing_mask = masker(with_indices, bc_mask, missing_mask, start, gshape)
+        return bc_mask, missing_mask
+
+    # ------------------------------------------------------------------ BC table
+    def build_bc_table(self, field_shape):
+        """256 ``XlbBcEntry`` rows (row = bc id) on the device."""
+        table = np.zeros(256, dtype=_lib.BC_ENTRY_DTYPE)
+        n_bc = 0
+        for bc in self.boundary_conditions:
+            if not (1 <= bc.id <= 253):
+                raise ValueError(f"boundary-condition id {bc.id} does not fit bc_mask (1..253)")
+            bc.bc_table_row(table[bc.id], field_shape)
+            n_bc = max(n_bc, bc.id + 1)
+        dev = torch.from_numpy(table.view(np.uint8).copy()).to(current_device())
+        return dev, n_bc
+
+    def _get_plan(self, f_0):
+        key = (tuple(f_0.shape), f_0.dtype, tuple(bc.id for bc in self.boundary_conditions))
+        if self._plan is None or self._plan[0] != key:
+            halo = getattr(self.grid, "halo", 0)
+            dom = self._domain(f_0, x_periodic=0 if halo else 1)
+            table, n_bc = self.build_bc_table(tuple(f_0.shape[1:]))
+            x_begin, x_end = (halo, dom.nx - halo) if self.velocity_set.d == 3 else (0, dom.nx)
+            self._plan = (key, dom, table, n_bc, x_begin, x_end)
+        return self._plan
+
+    # ------------------------------------------------------------------ the step
+    @Operator.register_backend(ComputeBackend.CUDA)
+    def cuda_implementation(self, f_0, f_1, bc_mask, missing_mask, omega, timestep):
+        q = self.velocity_set.q
+        if f_0.dtype != self.store_dtype or f_1.dtype != self.store_dtype:
+            raise ValueError(f"populations must be stored as {self.store_dtype} under policy {self.precision_policy.name}")
+        self._check_field(f_0, "f_0", q)
+        self._check_field(f_1, "f_1", q)
+        if f_0.shape != f_1.shape:
+            raise ValueError("f_0 and f_1 must have the same shape")
+        _, dom, table, n_bc, x_begin, x_end = self._get_plan(f_0)
+        if n_bc:
+            self._check_field(bc_mask, "bc_mask", 1)
+            self._check_field(missing_mask, "missing_mask", q)
+        rc = lib().xlb_step(
+            byref(dom), self.collision.abi_model, f_0.data_ptr(), f_1.data_ptr(),
+            bc_mask.data_ptr() if n_bc else None, missing_mask.data_ptr() if n_bc else None, table.data_ptr() if n_bc else None, n_bc,
+            float(omega), int(timestep), x_begin, x_end, self.kernel_variant, stream_ptr(),
+        )
+        check(rc, "IncompressibleNavierStokesStepper")
+        return f_0, f_1
