@@ -1,0 +1,434 @@
+#!/usr/bin/env python
+"""bench.py -- MLUPS of the fused LBM step (BASELINE.json metric) on N B200s of one node.
+
+    python bench.py --gpus 1 --steps K --warmup W            # this repo's CUDA path
+    python bench.py --impl reference --steps K --warmup W    # the reference's CPU path (oracle port), host cores
+    torchrun ... bench.py --gpus N ...                       # N ranks, x-slab decomposition, NCCL halo ring
+
+A "step" is one pass of the hot path (``IncompressibleNavierStokesStepper.__call__``: pull-stream + BCs +
+macroscopic + equilibrium + collide) over the whole lattice.  One JSON line is printed by rank 0.
+
+Keys beyond the base contract: ``roofline`` (algorithmic bytes / measured kernel time vs the measured HBM
+copy peak of MEASURED_PEAKS.json), ``cpu_baseline`` (the NumPy oracle port on this box's host cores, bounded
+sample), ``e2e`` (same metric with HOST buffers: pinned host -> device copy of the populations, the step,
+device -> host copy of the result, all inside the timed region).
+"""
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "MLUPS"
+UNIT = "MLUPS (1e6 lattice-cell updates / s)"
+
+WORKLOADS = {
+    # name: (lattice, collision, policy, shape, omega, case builder name)
+    "cavity512_d3q19_bgk_fp32": ("D3Q19", "BGK", "FP32FP32", (512, 512, 512), 1.0, "cavity"),
+    "cavity512_d3q19_bgk_fp64": ("D3Q19", "BGK", "FP64FP64", (512, 512, 512), 1.0, "cavity"),
+    "cavity128_d3q19_bgk_fp32": ("D3Q19", "BGK", "FP32FP32", (128, 128, 128), 1.0, "cavity"),
+    "cavity256_d3q19_bgk_fp32": ("D3Q19", "BGK", "FP32FP32", (256, 256, 256), 1.0, "cavity"),
+    "sphere384_d3q27_kbc_fp32": ("D3Q27", "KBC", "FP32FP32", (384, 128, 128), 1.6, "sphere"),
+    "sphere768_d3q27_kbc_fp32": ("D3Q27", "KBC", "FP32FP32", (768, 256, 256), 1.6, "sphere"),
+    "cavity1024_d3q19_bgk_fp16": ("D3Q19", "BGK", "FP32FP16", (1024, 1024, 1024), 1.0, "cavity"),
+    "cavity640_d3q19_bgk_fp16": ("D3Q19", "BGK", "FP32FP16", (640, 640, 640), 1.0, "cavity"),
+}
+STORE_BYTES = {"FP32FP32": 4, "FP64FP64": 8, "FP32FP16": 2, "FP64FP32": 4, "FP64FP16": 2}
+DTYPE_NAME = {"FP32FP32": "f32", "FP64FP64": "f64", "FP32FP16": "f32 (f16 storage)", "FP64FP32": "f64 (f32 storage)", "FP64FP16": "f64 (f16 storage)"}
+
+
+def b_alg(q, policy):
+    """Algorithmic bytes per cell update: q reads + q writes in the store dtype + 1 bc_mask byte."""
+    return 2 * q * STORE_BYTES[policy] + 1
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as fh:
+            return float(json.load(fh)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# --------------------------------------------------------------------------- clocks sampling
+class ClockSampler:
+    QUERY = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index=0):
+        self.index = index
+        self.rows = []
+        self._stop = threading.Event()
+        self._t = None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(
+                    ["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits", "-i", str(self.index)],
+                    capture_output=True, text=True, timeout=5,
+                ).stdout.strip()
+                if out:
+                    self.rows.append([c.strip() for c in out.split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def start(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._t:
+            self._t.join(timeout=6)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+            except Exception:
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {
+            "sm_mhz": sm[len(sm) // 2] if sm else None,
+            "sm_max_mhz": max(mx) if mx else None,
+            "reasons": sorted(reasons),
+            "samples": len(sm),
+        }
+
+
+# --------------------------------------------------------------------------- case construction (product objects)
+def build_case(workload, local_shape=None, slab=None):
+    """Product-side objects of a workload.  BC index sets are generated per slab (global coords) so that the
+    1536^3-class cases never materialise a global index list on one rank."""
+    import numpy as np
+
+    import xlb_b200 as xlb
+    from xlb_b200.compute_backend import ComputeBackend
+    from xlb_b200.operator.boundary_condition import (
+        EquilibriumBC, ExtrapolationOutflowBC, FullwayBounceBackBC, HalfwayBounceBackBC, ZouHeBC,
+    )
+    from xlb_b200.operator.stepper import IncompressibleNavierStokesStepper
+    from xlb_b200.precision_policy import PrecisionPolicy
+
+    lattice, collision, policy, shape, omega, kind = WORKLOADS[workload]
+    pol = PrecisionPolicy[policy]
+    vs = getattr(xlb.velocity_set, lattice)(precision_policy=pol, compute_backend=ComputeBackend.CUDA)
+    xlb.init(velocity_set=vs, default_backend=ComputeBackend.CUDA, default_precision_policy=pol)
+    if slab is not None:
+        grid = slab.make_grid(shape)
+    else:
+        grid = xlb.grid.grid_factory(shape, compute_backend=ComputeBackend.CUDA)
+    nx, ny, nz = shape
+    box = grid.bounding_box_indices()
+    box_ne = grid.bounding_box_indices(remove_edges=True)
+
+    def union(names):
+        idx = np.concatenate([np.array(box[n]) for n in names], axis=1)
+        return np.unique(idx, axis=-1)
+
+    if kind == "cavity":  # examples/performance/mlups_3d.py:194-204
+        bcs = [
+            EquilibriumBC(rho=1.0, u=(0.02, 0.0, 0.0), indices=box_ne["top"]),
+            FullwayBounceBackBC(indices=union(["bottom", "left", "right", "front", "back"])),
+        ]
+    else:  # examples/cfd/flow_past_sphere_3d.py:38-113 with Zou-He inlet (BASELINE config 3)
+        r = ny // 12
+        cx, cy, cz = nx // 6, ny // 2, nz // 2
+        xs = np.arange(max(cx - r, 0), min(cx + r + 1, nx))
+        X, Y, Z = np.meshgrid(xs, np.arange(ny), np.arange(nz), indexing="ij")
+        sel = (X - cx) ** 2 + (Y - cy) ** 2 + (Z - cz) ** 2 < r**2
+        sphere = np.stack([X[sel], Y[sel], Z[sel]])
+        bcs = [
+            FullwayBounceBackBC(indices=union(["bottom", "top", "front", "back"])),
+            ZouHeBC("velocity", prescribed_value=(0.04, 0.0, 0.0), indices=box_ne["left"]),
+            ExtrapolationOutflowBC(indices=box_ne["right"]),
+            HalfwayBounceBackBC(indices=sphere),
+        ]
+    stepper = IncompressibleNavierStokesStepper(grid=grid, boundary_conditions=bcs, collision_type=collision)
+    return stepper, vs, pol, shape, omega
+
+
+# --------------------------------------------------------------------------- CPU legs (the only users of oracle/)
+def cpu_baseline(workload, budget_s=20.0, max_steps=8):
+    """The NumPy oracle port of the reference's JAX step, timed on this box's host cores on a bounded sample:
+    the same BCs / lattice / policy at 128^3 (BASELINE config 1 when the workload is the cavity)."""
+    import numpy as np
+
+    from oracle import cases
+
+    lattice, collision, policy, shape, omega, kind = WORKLOADS[workload]
+    n = 128 if kind == "cavity" else None
+    if kind == "cavity":
+        case = cases.cavity3d(n, policy=policy, lattice=lattice, collision=collision, omega=omega)
+    else:
+        case = cases.sphere3d((96, 64, 64), policy=policy, lattice=lattice, collision=collision, omega=omega)
+    st, _ = cases.build_oracle(case)
+    f0, f1, bc, mm = st.prepare_fields()
+    f0 = f0.astype(st.sdt)
+    ncell = int(np.prod(case["shape"]))
+    f0, f1 = st(f0, f1, bc, mm, omega, 0)  # warm-up (page faults, caches)
+    f0, f1 = f1, f0
+    t0 = time.perf_counter()
+    steps = 0
+    while steps < max_steps and (time.perf_counter() - t0) < budget_s:
+        f0, f1 = st(f0, f1, bc, mm, omega, steps + 1)
+        f0, f1 = f1, f0
+        steps += 1
+    dt = time.perf_counter() - t0
+    return {
+        "value": ncell * steps / dt / 1e6,
+        "unit": UNIT,
+        "cores": 1,
+        "kind": "port",
+        "sample": f"{steps} steps of {case['name']} ({ncell} cells), NumPy oracle port of nse_stepper.py:238-282, single thread; host has {os.cpu_count()} cores",
+        "seconds": dt,
+    }
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path (oracle port; the reference itself needs jax, absent here)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    workload = args.workload
+    lattice, collision, policy, shape, omega, kind = WORKLOADS[workload]
+    base = cpu_baseline(workload, budget_s=max(20.0, 6.0 * args.steps), max_steps=max(args.steps, 1))
+    line = {
+        "impl": "reference",
+        "metric": METRIC,
+        "value": base["value"],
+        "unit": UNIT,
+        "n_gpus": args.gpus,
+        "steps": args.steps,
+        "warmup": args.warmup,
+        "ms_per_step": None,
+        "higher_is_better": True,
+        "scaling": "weak",
+        "vs_baseline": None,
+        "dtype": DTYPE_NAME[policy],
+        "data": "synthetic",
+        "config": {"workload": workload, "lattice": lattice, "collision": collision, "policy": policy, "shape": list(shape), "omega": omega},
+        "cpu_baseline": {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# --------------------------------------------------------------------------- native arm
+def run_native(args):
+    import torch
+    import torch.distributed as dist
+
+    from xlb_b200 import _lib
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device (xlb_b200 has no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    slab = None
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        from xlb_b200.distribute import SlabDecomposition
+
+        slab = SlabDecomposition(rank=rank, world=world)
+
+    workload = args.workload
+    lattice, collision, policy, shape, omega, kind = WORKLOADS[workload]
+    stepper, vs, pol, shape, omega = build_case(workload, slab=slab)
+    if slab is not None:
+        from xlb_b200.distribute import distribute
+
+        stepper = distribute(stepper, stepper.grid, vs, overlap=not args.no_overlap)
+    f_0, f_1, bc_mask, missing = stepper.prepare_fields()
+    ncell = shape[0] * shape[1] * shape[2]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- warm-up
+    t = 0
+    for _ in range(max(args.warmup, 3)):
+        f_0, f_1 = stepper(f_0, f_1, bc_mask, missing, omega, t)
+        f_0, f_1 = f_1, f_0
+        t += 1
+    barrier()
+
+    # ---- timed region: exactly K steps, CUDA events on the launching stream
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    launches0 = _lib.launch_count()
+    ev0 = torch.cuda.Event(enable_timing=True)
+    ev1 = torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    for _ in range(args.steps):
+        f_0, f_1 = stepper(f_0, f_1, bc_mask, missing, omega, t)
+        f_0, f_1 = f_1, f_0
+        t += 1
+    ev1.record()
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    launches = _lib.launch_count() - launches0
+    if world > 1:
+        tt = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms = float(tt.item())
+    clocks = sampler.stop() if rank == 0 else None
+    mlups = ncell * args.steps / (ms * 1e-3) / 1e6
+    finite = bool(torch.isfinite(f_0.float().sum()).item())
+
+    # ---- roofline of the dominant (only) kernel: per-launch CUDA-event time on the launching stream
+    peak, peak_src = measured_peaks()
+    roofline = None
+    if world == 1:
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(min(args.steps, 10))]
+        torch.cuda.synchronize()
+        for a, b in evs:
+            a.record()
+            f_0, f_1 = stepper(f_0, f_1, bc_mask, missing, omega, t)
+            b.record()
+            f_0, f_1 = f_1, f_0
+            t += 1
+        torch.cuda.synchronize()
+        per = sorted(a.elapsed_time(b) for a, b in evs)
+        k_ms = sum(per) / len(per)
+        bytes_per_launch = b_alg(vs.q, policy) * ncell
+        achieved = bytes_per_launch / (k_ms * 1e-3) / 1e9
+        roofline = {
+            "bound": "hbm",
+            "kernel": "step_vector_kernel",
+            "achieved": achieved,
+            "peak": peak,
+            "unit": "GB/s",
+            "frac": achieved / peak,
+            "traffic": None,
+            "bytes_per_cell": b_alg(vs.q, policy),
+            "cells_per_launch": ncell,
+            "kernel_ms": k_ms,
+            "peak_source": peak_src,
+        }
+
+    # ---- e2e: HOST buffers in, HOST buffers out (pinned), copies inside the timed region
+    e2e = None
+    if world == 1 and not args.no_e2e:
+        e2e = run_e2e(stepper, f_0, f_1, bc_mask, missing, omega, t, ncell, max(1, min(args.steps, args.e2e_steps)))
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+    line = {
+        "metric": METRIC,
+        "value": mlups,
+        "unit": UNIT,
+        "n_gpus": world,
+        "steps": args.steps,
+        "warmup": max(args.warmup, 3),
+        "ms_per_step": ms / args.steps,
+        "higher_is_better": True,
+        "scaling": "strong" if world > 1 else "weak",
+        "vs_baseline": None,
+        "dtype": DTYPE_NAME[policy],
+        "data": "synthetic",
+        "config": {
+            "workload": workload, "lattice": lattice, "collision": collision, "policy": policy, "shape": list(shape), "omega": omega,
+            "decomposition": f"x-slab x{world}" if world > 1 else "single block",
+            "l2": "inputs larger than L2 (two population buffers of %.1f GB each)" % (vs.q * ncell * STORE_BYTES[policy] / world / 1e9),
+        },
+        "gpu_launches": int(launches),
+        "finite": finite,
+        "clocks": clocks,
+    }
+    if roofline:
+        line["roofline"] = roofline
+    if e2e:
+        line["e2e"] = e2e
+    if world == 1 and not args.no_cpu_baseline:
+        base = cpu_baseline(workload)
+        line["cpu_baseline"] = {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def run_e2e(stepper, f_0, f_1, bc_mask, missing, omega, t, ncell, steps):
+    """Same metric with HOST buffers: every step copies the populations pinned-host -> device, runs the step and
+    copies the result device -> pinned-host (masks / BC tables are static and stay resident)."""
+    import torch
+
+    h_in = torch.empty(f_0.shape, dtype=f_0.dtype, pin_memory=True)
+    h_out = torch.empty(f_1.shape, dtype=f_1.dtype, pin_memory=True)
+    h_in.copy_(f_0)
+    torch.cuda.synchronize()
+    ev0 = torch.cuda.Event(enable_timing=True)
+    ev1 = torch.cuda.Event(enable_timing=True)
+    # one untimed pass
+    f_0.copy_(h_in, non_blocking=True)
+    stepper(f_0, f_1, bc_mask, missing, omega, t)
+    h_out.copy_(f_1, non_blocking=True)
+    torch.cuda.synchronize()
+    ev0.record()
+    for i in range(steps):
+        f_0.copy_(h_in, non_blocking=True)
+        stepper(f_0, f_1, bc_mask, missing, omega, t + 1 + i)
+        h_out.copy_(f_1, non_blocking=True)
+        h_in, h_out = h_out, h_in
+    ev1.record()
+    torch.cuda.synchronize()
+    ms = ev0.elapsed_time(ev1)
+    nbytes = f_0.numel() * f_0.element_size()
+    return {
+        "value": ncell * steps / (ms * 1e-3) / 1e6,
+        "unit": UNIT,
+        "h2d_bytes_per_step": int(nbytes),
+        "d2h_bytes_per_step": int(nbytes),
+        "steps": steps,
+        "ms_per_step": ms / steps,
+        "note": "populations pinned-host -> device, xlb_step, device -> pinned-host every step",
+    }
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS))
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-steps", type=int, default=4)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-overlap", action="store_true")
+    args = ap.parse_args()
+    if args.workload is None:
+        # N=1: BASELINE configs[1] (512^3 D3Q19 BGK FP32FP32).  N>1: configs[3] (1024^3 FP32FP16, strong scaling).
+        args.workload = "cavity512_d3q19_bgk_fp32" if args.gpus == 1 else "cavity1024_d3q19_bgk_fp16"
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_native(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

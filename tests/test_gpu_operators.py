@@ -1,0 +1,117 @@
+"""Stand-alone operators on the GPU (through the C ABI) vs the oracle, plus the reference's analytic tests."""
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import ops
+from oracle.lattice import make_lattice
+from tests.util import init_xlb, rel_err, to_dev, to_np
+
+pytestmark = pytest.mark.gpu
+
+LATS = [("D2Q9", (50, 36)), ("D3Q19", (20, 18, 16)), ("D3Q27", (20, 18, 17))]
+POL = [("FP32FP32", np.float32, 2e-6), ("FP64FP64", np.float64, 1e-14)]
+
+
+def _rand_f(lat, shape, dt, seed=0):
+    rng = np.random.default_rng(seed)
+    w = lat.w.reshape((-1,) + (1,) * lat.d)
+    return (w * (1.0 + 0.05 * rng.uniform(-1, 1, (lat.q,) + shape))).astype(dt)
+
+
+@pytest.mark.parametrize("name,shape", LATS)
+@pytest.mark.parametrize("policy,dt,tol", POL)
+def test_equilibrium_macroscopic(name, shape, policy, dt, tol):
+    from xlb_b200.operator.equilibrium import QuadraticEquilibrium
+    from xlb_b200.operator.macroscopic import FirstMoment, Macroscopic, SecondMoment, ZeroMoment
+
+    init_xlb(name, policy)
+    lat = make_lattice(name)
+    rng = np.random.default_rng(1)
+    rho = (1.0 + 0.1 * rng.uniform(-1, 1, (1,) + shape)).astype(dt)
+    u = (0.1 * rng.uniform(-1, 1, (lat.d,) + shape)).astype(dt)
+    feq_o = ops.quadratic_equilibrium(lat, rho, u, dtype=dt)
+    feq = QuadraticEquilibrium()(to_dev(rho), to_dev(u))
+    assert feq.dtype == to_dev(rho).dtype and tuple(feq.shape) == feq_o.shape
+    assert rel_err(to_np(feq), feq_o) <= tol
+    # out-parameter form
+    out = torch.empty_like(feq)
+    QuadraticEquilibrium()(to_dev(rho), to_dev(u), out)
+    assert torch.equal(out, feq)
+    # moments
+    f = _rand_f(lat, shape, dt)
+    rho_o, u_o = ops.macroscopic(lat, f)
+    r, v = Macroscopic()(to_dev(f))
+    assert rel_err(to_np(r), rho_o) <= tol
+    assert np.max(np.abs(to_np(v) - u_o)) <= 10 * tol
+    assert torch.equal(ZeroMoment()(to_dev(f)), r)
+    assert torch.equal(FirstMoment()(to_dev(f), r), v)
+    pi_o = ops.second_moment(lat, f)
+    pi = SecondMoment()(to_dev(f))
+    assert tuple(pi.shape) == pi_o.shape
+    assert rel_err(to_np(pi), pi_o) <= 4 * tol
+
+
+@pytest.mark.parametrize("name,shape", LATS)
+def test_reference_analytic_identities(name, shape):
+    """feq(1,0)=w and moments(feq(rho,u))=(rho,u) (reference tests/kernels/{equilibrium,macroscopic})."""
+    from xlb_b200.operator.equilibrium import QuadraticEquilibrium
+    from xlb_b200.operator.macroscopic import Macroscopic
+
+    vs, _ = init_xlb(name, "FP32FP32")
+    g = __import__("xlb_b200").grid.grid_factory(shape)
+    rho = g.create_field(cardinality=1, fill_value=1.0)
+    u = g.create_field(cardinality=vs.d, fill_value=0.0)
+    feq = QuadraticEquilibrium()(rho, u)
+    w = torch.tensor(vs.w, dtype=torch.float32, device=feq.device).reshape((-1,) + (1,) * vs.d)
+    assert torch.allclose(feq, w.expand_as(feq))
+    assert torch.allclose(feq.sum(0), torch.ones_like(feq[0]))
+    rho = g.create_field(cardinality=1, fill_value=1.1)
+    u = g.create_field(cardinality=vs.d, fill_value=1.0)
+    r, v = Macroscopic()(QuadraticEquilibrium()(rho, u))
+    assert np.allclose(to_np(r), 1.1)
+    assert np.allclose(to_np(v), 1.0, atol=1e-6)
+
+
+@pytest.mark.parametrize("name,shape", LATS)
+@pytest.mark.parametrize("policy,dt,tol", POL)
+@pytest.mark.parametrize("omega", [0.6, 1.0, 1.9])
+def test_collision(name, shape, policy, dt, tol, omega):
+    from xlb_b200.operator.collision import BGK, KBC
+
+    init_xlb(name, policy)
+    lat = make_lattice(name)
+    f = _rand_f(lat, shape, dt, 2)
+    rho, u = ops.macroscopic(lat, f)
+    feq = ops.quadratic_equilibrium(lat, rho, u, dtype=dt)
+    out = BGK()(to_dev(f), to_dev(feq), omega)
+    assert rel_err(to_np(out), ops.bgk(f, feq, omega)) <= tol
+    if name == "D3Q19":
+        with pytest.raises(NotImplementedError):
+            KBC()
+        return
+    out_o = ops.kbc(lat, f, feq, omega)
+    out = KBC()(to_dev(f), to_dev(feq), omega)
+    assert rel_err(to_np(out), out_o) <= 20 * tol  # the entropic ratio sp1/sp2 amplifies rounding of fneq
+    buf = torch.empty_like(out)
+    KBC()(to_dev(f), to_dev(feq), buf, omega)
+    assert torch.equal(buf, out)
+
+
+@pytest.mark.parametrize("name,shape", LATS + [("D3Q19", (5, 4, 3)), ("D3Q27", (1, 1, 1))])
+@pytest.mark.parametrize("dt", [np.float32, np.float64, np.float16, np.bool_])
+def test_stream_bit_exact(name, shape, dt):
+    from xlb_b200.operator.stream import Stream
+
+    init_xlb(name, "FP32FP32")
+    lat = make_lattice(name)
+    rng = np.random.default_rng(3)
+    f = rng.uniform(0, 1, (lat.q,) + shape)
+    f = (f > 0.5) if dt is np.bool_ else f.astype(dt)
+    out = Stream()(to_dev(f))
+    assert np.array_equal(to_np(out), ops.stream(lat, f))
+    # the reference's one-hot plane test
+    g = np.zeros((lat.q,) + shape, np.float32)
+    g[..., shape[-1] // 2] = 1
+    assert np.array_equal(to_np(Stream()(to_dev(g))), ops.stream(lat, g))

@@ -1,0 +1,160 @@
+"""The fused step kernel (xlb_step through the C ABI) vs the oracle's restatement of
+IncompressibleNavierStokesStepper.jax_implementation_pull (nse_stepper.py:238-282).
+
+Tolerances (BASELINE.json): relative to max|f|; one step <= 1e-6 FP32 / 1e-13 FP64 / 1 fp16 ulp,
+N steps <= 1e-5 FP32 / 1e-12 FP64.
+"""
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import cases
+from tests.util import TOL_N_STEP, TOL_ONE_STEP, build_product, rel_err, to_dev, to_np
+from xlb_b200 import _lib
+
+pytestmark = pytest.mark.gpu
+
+ONE_STEP = [
+    cases.periodic((16, 12, 8)),
+    cases.periodic((9, 7, 5), lattice="D3Q27", collision="KBC"),  # odd extents -> scalar kernel
+    cases.periodic((16, 12, 8), lattice="D3Q27", collision="KBC", policy="FP64FP64"),
+    cases.cavity3d(16),
+    cases.cavity3d(16, omega=1.7),
+    cases.cavity3d(16, policy="FP64FP64", omega=1.7),
+    cases.cavity3d(16, policy="FP32FP16", omega=1.7),
+    cases.cavity3d(16, policy="FP64FP32", omega=1.7),
+    cases.cavity3d(16, policy="FP64FP16", omega=1.7),
+    cases.cavity3d(0, shape=(10, 12, 16), lattice="D3Q27", collision="KBC", omega=1.8),
+    cases.cavity3d(0, shape=(7, 9, 11), omega=1.3),
+    cases.cavity2d(24),
+    cases.cavity2d(24, collision="KBC", policy="FP64FP64"),
+    cases.cavity2d(0, shape=(21, 13), collision="KBC"),
+    cases.sphere3d((48, 24, 24)),
+    cases.sphere3d((48, 24, 24), policy="FP64FP64"),
+    cases.sphere3d((48, 24, 24), policy="FP32FP16"),
+    cases.sphere3d((48, 24, 24), profile=True),
+    cases.sphere3d((40, 24, 20), lattice="D3Q19", collision="BGK", inlet="pressure", outlet="pressure"),
+    cases.sphere3d((36, 24, 24), outlet="donothing", moving_sphere=(0.01, 0.0, 0.005)),
+    cases.sphere3d((36, 20, 20), policy="FP64FP64", inlet="pressure", outlet="extrapolation"),
+]
+VARIANTS = [_lib.VARIANT_AUTO, _lib.VARIANT_SCALAR, _lib.VARIANT_GENERIC]
+
+
+def _one_step(case, variant, seed=0):
+    ost, _ = cases.build_oracle(case)
+    _, _, bc_o, mm_o = ost.prepare_fields()
+    st, _ = build_product(case, backend_config={"kernel_variant": variant})
+    _, f_1, bc_mask, missing = st.prepare_fields()
+    assert np.array_equal(to_np(bc_mask), bc_o) and np.array_equal(to_np(missing), mm_o)
+    f0 = cases.random_state(case, seed=seed)
+    _, ref = ost(f0, None, bc_o, mm_o, case["omega"], 0)
+    f_0 = to_dev(f0)
+    out0, out1 = st(f_0, f_1, bc_mask, missing, case["omega"], 0)
+    assert out1.data_ptr() == f_1.data_ptr() and out0.data_ptr() == f_0.data_ptr()
+    assert np.array_equal(to_np(f_0), f0), "f_0 must not be modified by the step"
+    return to_np(out1), ref
+
+
+@pytest.mark.parametrize("variant", VARIANTS, ids=["auto", "scalar", "generic"])
+@pytest.mark.parametrize("case", ONE_STEP, ids=lambda c: c["name"])
+def test_one_step_parity(case, variant):
+    got, ref = _one_step(case, variant)
+    assert got.dtype == ref.dtype
+    tol = TOL_ONE_STEP[case["policy"]]
+    if case["collision"] == "KBC":
+        tol *= 4  # gamma = f(sp1/sp2) amplifies rounding differences of the summation order
+    err = rel_err(got, ref)
+    assert err <= tol, f"{case['name']}: rel err {err:.3e} > {tol:.1e}"
+
+
+@pytest.mark.parametrize("case", [c for c in ONE_STEP if c["policy"] in ("FP32FP32", "FP64FP64")][:8], ids=lambda c: c["name"])
+def test_variants_agree_bitwise(case):
+    """The vector, scalar and generic kernels perform the same per-cell arithmetic."""
+    a, _ = _one_step(case, _lib.VARIANT_AUTO)
+    b, _ = _one_step(case, _lib.VARIANT_SCALAR)
+    c, _ = _one_step(case, _lib.VARIANT_GENERIC)
+    assert np.array_equal(a, b)
+    assert np.array_equal(a, c)
+
+
+N_STEP = [
+    (cases.cavity3d(24, omega=1.0), 100),
+    (cases.cavity3d(24, omega=1.7), 100),
+    (cases.cavity3d(24, omega=1.7, policy="FP64FP64"), 100),
+    (cases.cavity2d(32), 100),
+    (cases.sphere3d((48, 24, 24)), 200),
+    (cases.sphere3d((48, 24, 24), policy="FP64FP64"), 200),
+    (cases.sphere3d((48, 24, 24), profile=True, lattice="D3Q19", collision="BGK", omega=1.5), 100),
+]
+
+
+@pytest.mark.parametrize("case,nsteps", N_STEP, ids=lambda v: v["name"] if isinstance(v, dict) else str(v))
+def test_n_step_parity(case, nsteps):
+    ost, _ = cases.build_oracle(case)
+    f0, f1, bc_o, mm_o = ost.prepare_fields()
+    ref, _ = ost.run(f0.astype(ost.sdt), f1, bc_o, mm_o, case["omega"], nsteps)
+    st, _ = build_product(case)
+    f_0, f_1, bc_mask, missing = st.prepare_fields()
+    for i in range(nsteps):
+        f_0, f_1 = st(f_0, f_1, bc_mask, missing, case["omega"], i)
+        f_0, f_1 = f_1, f_0
+    err = rel_err(to_np(f_0), ref)
+    tol = TOL_N_STEP[case["policy"]]
+    assert np.isfinite(to_np(f_0)).all()
+    assert err <= tol, f"{case['name']}: {nsteps}-step rel err {err:.3e} > {tol:.1e}"
+
+
+def test_fp16_storage_n_step():
+    """FP32FP16: N-step <= 5e-3 relative on rho, <= 5e-3 * u_lid absolute on u."""
+    from oracle import ops
+    from oracle.lattice import make_lattice
+
+    case = cases.cavity3d(24, policy="FP32FP16", omega=1.7)
+    lat = make_lattice(case["lattice"])
+    ost, _ = cases.build_oracle(case)
+    f0, f1, bc_o, mm_o = ost.prepare_fields()
+    ref, _ = ost.run(f0.astype(ost.sdt), f1, bc_o, mm_o, case["omega"], 50)
+    st, _ = build_product(case)
+    f_0, f_1, bc_mask, missing = st.prepare_fields()
+    assert f_0.dtype == torch.float16
+    for i in range(50):
+        f_0, f_1 = st(f_0, f_1, bc_mask, missing, case["omega"], i)
+        f_0, f_1 = f_1, f_0
+    rho_r, u_r = ops.macroscopic(lat, ref.astype(np.float32))
+    rho_g, u_g = ops.macroscopic(lat, to_np(f_0).astype(np.float32))
+    assert np.max(np.abs(rho_g - rho_r)) <= 5e-3
+    assert np.max(np.abs(u_g - u_r)) <= 5e-3 * 0.02 + 1e-4
+
+
+def test_slab_launches_equal_whole_launch():
+    """xlb_step on x sub-ranges (what the multi-GPU overlap schedule issues) == one whole-grid launch, bitwise."""
+    case = cases.sphere3d((48, 24, 24))
+    st, _ = build_product(case)
+    _, f_1, bc_mask, missing = st.prepare_fields()
+    f_0 = to_dev(cases.random_state(case, seed=5))
+    st(f_0, f_1, bc_mask, missing, case["omega"], 0)
+    whole = f_1.clone()
+    f_1.zero_()
+    _, dom, table, n_bc, _, _ = st._get_plan(f_0)
+    from ctypes import byref
+
+    for xb, xe in [(0, 1), (1, 47), (47, 48)]:
+        rc = _lib.lib().xlb_step(byref(dom), st.collision.abi_model, f_0.data_ptr(), f_1.data_ptr(), bc_mask.data_ptr(), missing.data_ptr(),
+                                 table.data_ptr(), n_bc, float(case["omega"]), 0, xb, xe, 0, _lib.current_stream_ptr())
+        _lib.check(rc, "xlb_step")
+    assert torch.equal(whole, f_1)
+
+
+def test_error_paths():
+    case = cases.cavity3d(8)
+    st, _ = build_product(case)
+    f_0, f_1, bc_mask, missing = st.prepare_fields()
+    with pytest.raises(ValueError):
+        st(f_0, f_0, bc_mask, missing, 1.0, 0)  # same buffer
+    with pytest.raises(ValueError):
+        st(f_0.double(), f_1, bc_mask, missing, 1.0, 0)  # wrong store dtype
+    with pytest.raises(ValueError):
+        st(f_0.cpu(), f_1, bc_mask, missing, 1.0, 0)  # host tensor: no CPU path
+    with pytest.raises(ValueError):
+        st(f_0[:, ::2], f_1[:, ::2], bc_mask, missing, 1.0, 0)  # non-contiguous
