@@ -30,7 +30,7 @@ def cavity3d(n, policy="FP32FP32", lattice="D3Q19", collision="BGK", omega=1.0, 
     lid = box_ne["top"]
     walls = _union(box, ["bottom", "left", "right", "front", "back"], 3)
     return dict(
-        name=f"cavity3d_{'x'.join(map(str, shape))}_{lattice}_{collision}_{policy}",
+        name=f"cavity3d_{'x'.join(map(str, shape))}_{lattice}_{collision}_{policy}_w{omega}",
         lattice=lattice,
         policy=policy,
         shape=shape,
@@ -50,7 +50,7 @@ def cavity2d(n, policy="FP32FP32", collision="BGK", omega=1.6, u_lid=0.05, shape
     lid = box_ne["top"]
     walls = _union(box, ["bottom", "left", "right"], 2)
     return dict(
-        name=f"cavity2d_{'x'.join(map(str, shape))}_{collision}_{policy}",
+        name=f"cavity2d_{'x'.join(map(str, shape))}_{collision}_{policy}_w{omega}",
         lattice="D2Q9",
         policy=policy,
         shape=shape,
@@ -127,7 +127,7 @@ def sphere3d(
     if moving_sphere is not None:
         sphere_bc["prescribed_value"] = tuple(moving_sphere)
     return dict(
-        name=f"sphere3d_{'x'.join(map(str, shape))}_{lattice}_{collision}_{policy}_{inlet}_{outlet}{'_prof' if profile else ''}",
+        name=f"sphere3d_{'x'.join(map(str, shape))}_{lattice}_{collision}_{policy}_{inlet}_{outlet}{'_prof' if profile else ''}{'_moving' if moving_sphere is not None else ''}_w{omega}",
         lattice=lattice,
         policy=policy,
         shape=shape,
@@ -139,7 +139,7 @@ def sphere3d(
 
 def periodic(shape, policy="FP32FP32", lattice="D3Q19", collision="BGK", omega=1.7):
     return dict(
-        name=f"periodic_{'x'.join(map(str, shape))}_{lattice}_{collision}_{policy}",
+        name=f"periodic_{'x'.join(map(str, shape))}_{lattice}_{collision}_{policy}_w{omega}",
         lattice=lattice,
         policy=policy,
         shape=tuple(shape),
