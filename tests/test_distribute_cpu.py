@@ -1,0 +1,87 @@
+"""Multi-rank plumbing on CPU (gloo, world_size 2 and 3): slab partition, periodic ring, halo contents.
+The same HaloExchange object drives NCCL on the GPUs; the kernels are not involved here."""
+
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from oracle import ops
+from oracle.distribute import sharded_stream
+from oracle.lattice import make_lattice
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, lattice, shape, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from xlb_b200.distribute import HaloExchange, SlabDecomposition
+
+        lat = make_lattice(lattice)
+        rng = np.random.default_rng(7)
+        f = rng.uniform(0, 1, (lat.q,) + shape).astype(np.float32)
+        dec = SlabDecomposition()
+        assert (dec.rank, dec.world) == (rank, world)
+        x0, n = dec.local_range(shape[0])
+        slab = np.full((lat.q, n + 2) + shape[1:], np.nan, np.float32)
+        slab[:, 1:-1] = f[:, x0 : x0 + n]
+        t = torch.from_numpy(slab)
+        HaloExchange(dec, lat).exchange(t)
+        got = t.numpy()
+        ri, li = lat.right_indices, lat.left_indices
+        assert np.array_equal(got[ri, 0], f[ri, (x0 - 1) % shape[0]])
+        assert np.array_equal(got[li, n + 1], f[li, (x0 + n) % shape[0]])
+        # ghosts of the other populations stay untouched (only outgoing populations travel)
+        others = [l for l in range(lat.q) if l not in set(ri.tolist())]
+        assert np.isnan(got[others, 0]).all()
+        # pull-stream of the owned planes from slab + ghosts == global periodic stream
+        glob = ops.stream(lat, f)
+        local = np.empty((lat.q, n) + shape[1:], np.float32)
+        for l in range(lat.q):
+            cx, cy, cz = (int(v) for v in lat.c[:, l])
+            src = got[l, 1 - cx : 1 - cx + n]
+            local[l] = np.roll(src, (cy, cz), axis=(1, 2))
+        assert np.array_equal(local, glob[:, x0 : x0 + n])
+        open(os.path.join(out_dir, f"ok{rank}"), "w").write("ok")
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,lattice,shape", [(2, "D3Q19", (8, 5, 4)), (3, "D3Q27", (10, 4, 5)), (2, "D3Q27", (4, 3, 3))])
+def test_halo_ring_gloo(world, lattice, shape, tmp_path):
+    mp.spawn(_worker, args=(world, _free_port(), lattice, shape, str(tmp_path)), nprocs=world, join=True)
+    assert all((tmp_path / f"ok{r}").exists() for r in range(world))
+
+
+def test_slab_partition():
+    from xlb_b200.distribute import SlabDecomposition
+
+    for world in (1, 2, 3, 4, 8):
+        for nx in (16, 19, 64):
+            got = [SlabDecomposition(r, world).local_range(nx) for r in range(world)]
+            assert got[0][0] == 0 and sum(n for _, n in got) == nx
+            for (a, n), (b, _) in zip(got, got[1:]):
+                assert a + n == b
+    d = SlabDecomposition(0, 4)
+    assert (d.left, d.right) == (3, 1)
+    with pytest.raises(ValueError):
+        SlabDecomposition(1, 8).local_range(8)
+
+
+@pytest.mark.parametrize("lattice,shape,n", [("D3Q19", (8, 5, 4), 2), ("D3Q27", (12, 4, 3), 4)])
+def test_oracle_ring_equals_global_stream(lattice, shape, n):
+    """oracle/distribute.py (distribute.py:18-46 restated) == the global periodic roll."""
+    lat = make_lattice(lattice)
+    f = np.random.default_rng(1).uniform(0, 1, (lat.q,) + shape)
+    assert np.array_equal(sharded_stream(lat, f, n), ops.stream(lat, f))

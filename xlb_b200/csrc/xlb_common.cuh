@@ -172,6 +172,7 @@ struct StepParams {
     int x_begin, x_end;
     int x_periodic;
     int ntz;  // nz / V
+    int ntz_shift;  // log2(ntz) when ntz is a power of two, else -1
     long long qs;   // population stride (elements)
     long long mqs;  // missing-mask direction stride
     double omega;

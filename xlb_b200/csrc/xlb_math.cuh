@@ -115,64 +115,137 @@ XLB_D T kbc_delta_s(const T (&pi)[6]) {
     }
 }
 
+// ---------------------------------------------------------------------------- fused-kernel arithmetic
+// The fused step evaluates the same formulas as the reference but shares work between a direction L
+// and its opposite O (c_O = -c_L, w_O = w_L):
+//     feq_L = rw*(1 - usqr) + rw*cu + 0.5*rw*cu^2,   feq_O = rw*(1 - usqr) - rw*cu + 0.5*rw*cu^2,   rw = rho*w_L
+// and u = (sum c f) * (1/rho).  This differs from quadratic_equilibrium.py:25-30 / first_moment.py:16-18 only
+// in rounding (a few ulp of the compute type) -- the same freedom XLA takes when it fuses and contracts the
+// JAX expression -- and is covered by the parity tolerances (1e-6 one step / 1e-5 N steps FP32, 1e-13 / 1e-12 FP64).
+XLB_D float fast_div(float a, float b) { return __fdividef(a, b); }  // MUFU.RCP * a, <= 2 ulp
+XLB_D double fast_div(double a, double b) { return a / b; }
+XLB_D float rcp_of(float x) { return __frcp_rn(x); }
+XLB_D double rcp_of(double x) { return 1.0 / x; }
+
+template <typename T, int Q, int V, int J>
+XLB_D void moments_fused(const T (&f)[Q][V], T& rho, T (&u)[3]) {
+    T r = T(0), sx = T(0), sy = T(0), sz = T(0);
+    bool f0 = true, fx = true, fy = true, fz = true;
+    static_for<Q>([&](auto lc) {
+        XLB_IDX(l, lc);
+        using D = Dir<Q, l>;
+        const T v = f[l][J];
+        acc_signed<1>(r, f0, v);
+        acc_signed<D::cx>(sx, fx, v);
+        acc_signed<D::cy>(sy, fy, v);
+        acc_signed<D::cz>(sz, fz, v);
+    });
+    rho = r;
+    const T inv = rcp_of(r);
+    u[0] = (axis0<Q>() > 0) ? T(0) : sx * inv;
+    u[1] = sy * inv;
+    u[2] = sz * inv;
+}
+
+// cu = 3 c_L.u from the pre-scaled velocity u3 = 3u
+template <typename T, int Q, int L>
+XLB_D T cu_of(const T (&u3)[3]) {
+    using D = Dir<Q, L>;
+    T s = T(0);
+    bool first = true;
+    acc_signed<D::cx>(s, first, u3[0]);
+    acc_signed<D::cy>(s, first, u3[1]);
+    acc_signed<D::cz>(s, first, u3[2]);
+    return s;
+}
+
+// symmetric (even in c) and antisymmetric parts of feq for the pair (L, opp L); base = 1 - usqr
+template <typename T, int Q, int L>
+XLB_D void feq_pair(T rho, const T (&u3)[3], T base, T& even, T& odd) {
+    const T rw = rho * T(Dir<Q, L>::w);
+    const T cu = cu_of<T, Q, L>(u3);
+    even = rw * (T(0.5) * cu * cu + base);
+    odd = rw * cu;
+}
+
 // Collide column J in place.  If fullway is set the COLLISION-step FullwayBounceBackBC result
 // f_post[l] = f_post_stream[opp l] (bc_fullway_bounce_back.py:50-56) is selected instead.
 template <typename T, int Q, int COLL, int V, int J>
 XLB_D void collide_column(T (&f)[Q][V], T omega, bool fullway) {
     T rho, u[3];
-    moments<T, Q, V, J>(f, rho, u);
-    const T usqr = usqr_of<T>(u, axis0<Q>());
+    moments_fused<T, Q, V, J>(f, rho, u);
+    const T base = T(1.0) - usqr_of<T>(u, axis0<Q>());
+    const T u3[3] = {T(3.0) * u[0], T(3.0) * u[1], T(3.0) * u[2]};
     if (COLL == XLB_BGK) {
         static_for<Q>([&](auto lc) {
             XLB_IDX(l, lc);
             constexpr int o = Dir<Q, l>::o;
-            if (o >= l) {
+            if (o == l) {  // rest population: cu = 0
+                const T fl = f[l][J];
+                const T nl = fl - omega * (fl - rho * T(Dir<Q, l>::w) * base);
+                f[l][J] = fullway ? fl : nl;
+            } else if (o > l) {
+                T even, odd;
+                feq_pair<T, Q, l>(rho, u3, base, even, odd);
                 const T fl = f[l][J], fo = f[o][J];
-                const T nl = fl - omega * (fl - feq_dir<T, Q, l>(rho, u, usqr));
+                const T nl = fl - omega * (fl - (even + odd));
+                const T no = fo - omega * (fo - (even - odd));
                 f[l][J] = fullway ? fo : nl;
-                if (o != l) {
-                    const T no = fo - omega * (fo - feq_dir<T, Q, o>(rho, u, usqr));
-                    f[o][J] = fullway ? fl : no;
-                }
+                f[o][J] = fullway ? fl : no;
             }
         });
     } else {
-        // ---- KBC (kbc.py:40-79)
+        // ---- KBC (kbc.py:40-79).  Pi = sum cc fneq only sees the even part of fneq; delta_s is even too.
         T pi[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
         static_for<Q>([&](auto lc) {
             XLB_IDX(l, lc);
-            acc_second_moment<Q, l>(pi, f[l][J] - feq_dir<T, Q, l>(rho, u, usqr));
+            constexpr int o = Dir<Q, l>::o;
+            if (o > l) {
+                T even, odd;
+                feq_pair<T, Q, l>(rho, u3, base, even, odd);
+                acc_second_moment<Q, l>(pi, (f[l][J] + f[o][J]) - T(2.0) * even);
+            }
         });
         const T beta = T(0.5) * omega;
         const T inv_beta = T(1.0) / beta;
         T sp1 = T(0), sp2 = T(0);
         static_for<Q>([&](auto lc) {
             XLB_IDX(l, lc);
-            const T fe = feq_dir<T, Q, l>(rho, u, usqr);
-            const T ds = kbc_delta_s<T, Q, l>(pi);
-            const T dh = (f[l][J] - fe) - ds;
-            const T temp = dh / fe;
-            sp1 += temp * ds;
-            sp2 += temp * dh;
+            constexpr int o = Dir<Q, l>::o;
+            if (o == l) {
+                const T fe = rho * T(Dir<Q, l>::w) * base;
+                const T dh = f[l][J] - fe;  // delta_s of the rest direction is 0
+                sp2 += fast_div(dh, fe) * dh;
+            } else if (o > l) {
+                T even, odd;
+                feq_pair<T, Q, l>(rho, u3, base, even, odd);
+                const T ds = kbc_delta_s<T, Q, l>(pi);
+                const T fel = even + odd, feo = even - odd;
+                const T dhl = (f[l][J] - fel) - ds, dho = (f[o][J] - feo) - ds;
+                const T tl = fast_div(dhl, fel), to = fast_div(dho, feo);
+                sp1 += (tl + to) * ds;
+                sp2 += tl * dhl + to * dho;
+            }
         });
-        const T gamma = inv_beta - (T(2.0) - inv_beta) * sp1 / (T(1e-32) + sp2);
+        const T gamma = inv_beta - (T(2.0) - inv_beta) * fast_div(sp1, T(1e-32) + sp2);
         static_for<Q>([&](auto lc) {
             XLB_IDX(l, lc);
             constexpr int o = Dir<Q, l>::o;
-            if (o >= l) {
+            if (o == l) {
+                const T fl = f[l][J];
+                const T dh = fl - rho * T(Dir<Q, l>::w) * base;
+                const T nl = fl - beta * (gamma * dh);
+                f[l][J] = fullway ? fl : nl;
+            } else if (o > l) {
+                T even, odd;
+                feq_pair<T, Q, l>(rho, u3, base, even, odd);
+                const T ds = kbc_delta_s<T, Q, l>(pi);
                 const T fl = f[l][J], fo = f[o][J];
-                {
-                    const T ds = kbc_delta_s<T, Q, l>(pi);
-                    const T dh = (fl - feq_dir<T, Q, l>(rho, u, usqr)) - ds;
-                    const T nl = fl - beta * (T(2.0) * ds + gamma * dh);
-                    f[l][J] = fullway ? fo : nl;
-                }
-                if (o != l) {
-                    const T ds = kbc_delta_s<T, Q, o>(pi);
-                    const T dh = (fo - feq_dir<T, Q, o>(rho, u, usqr)) - ds;
-                    const T no = fo - beta * (T(2.0) * ds + gamma * dh);
-                    f[o][J] = fullway ? fl : no;
-                }
+                const T dhl = (fl - (even + odd)) - ds, dho = (fo - (even - odd)) - ds;
+                const T nl = fl - beta * (T(2.0) * ds + gamma * dhl);
+                const T no = fo - beta * (T(2.0) * ds + gamma * dho);
+                f[l][J] = fullway ? fo : nl;
+                f[o][J] = fullway ? fl : no;
             }
         });
     }

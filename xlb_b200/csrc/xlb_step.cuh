@@ -111,6 +111,21 @@ __global__ void __launch_bounds__(128) step_generic_kernel(const __grid_constant
 }
 
 // ------------------------------------------------------------------ fused vector kernel (K1)
+// predicated scalar load (no branch): returns *ptr where pred, else keep
+XLB_D float ld_if(const float* ptr, bool pred, float keep) {
+    asm("{ .reg .pred q; setp.ne.s32 q, %2, 0; @q ld.global.nc.f32 %0, [%1]; }" : "+f"(keep) : "l"(ptr), "r"((int)pred));
+    return keep;
+}
+XLB_D double ld_if(const double* ptr, bool pred, double keep) {
+    asm("{ .reg .pred q; setp.ne.s32 q, %2, 0; @q ld.global.nc.f64 %0, [%1]; }" : "+d"(keep) : "l"(ptr), "r"((int)pred));
+    return keep;
+}
+XLB_D __half ld_if(const __half* ptr, bool pred, __half keep) {
+    unsigned short k = __half_as_ushort(keep);
+    asm("{ .reg .pred q; setp.ne.s32 q, %2, 0; @q ld.global.nc.u16 %0, [%1]; }" : "+h"(k) : "l"(ptr), "r"((int)pred));
+    return __ushort_as_half(k);
+}
+
 template <typename T, typename S, int Q, int COLL, int V, int BLOCK, int MINB, bool HAS_BC>
 __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_constant__ StepParams p) {
     const S* __restrict__ f0 = static_cast<const S*>(p.f0);
@@ -120,11 +135,18 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_c
     const bool active = i < nvec;
     if (!active) i = nvec - 1;  // keep the lane alive for the shuffles
     const int x = p.x_begin + blockIdx.y;
-    const int y = i / p.ntz;
-    const int tz = i - y * p.ntz;
+    int y, tz;
+    if (p.ntz_shift >= 0) {
+        y = i >> p.ntz_shift;
+        tz = i & (p.ntz - 1);
+    } else {
+        y = i / p.ntz;
+        tz = i - y * p.ntz;
+    }
     const int z0 = tz * V;
     const int lane = threadIdx.x & 31;
-    const long long cell = ((long long)x * p.ny + y) * p.nz + z0;
+    const long long plane = (long long)p.ny * p.nz;
+    const long long cell = x * plane + (long long)y * p.nz + z0;
 
     // ---- packed bc ids of my V cells
     uint8_t ids[V];
@@ -156,34 +178,37 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_c
     const int xm = p.x_periodic ? wrap1(x - 1, p.nx) : x - 1;
     const int xp = p.x_periodic ? wrap1(x + 1, p.nx) : x + 1;
     const int ym = wrap1(y - 1, p.ny), yp = wrap1(y + 1, p.ny);
+    // element offsets of the source rows, indexed by c (0 -> same, +1 -> pull from the minus side, -1 -> plus side)
+    const long long ox0 = x * plane, oxm = xm * plane, oxp = xp * plane;
+    const int oy0 = y * p.nz, oym = ym * p.nz, oyp = yp * p.nz;
     const bool edge_lo = (lane == 0) || (tz == 0);
     const bool edge_hi = (lane == 31) || (tz == p.ntz - 1);
-    const int z_lo = (tz == 0) ? p.nz - 1 : z0 - 1;        // source of the element left of my vector
-    const int z_hi = (tz == p.ntz - 1) ? 0 : z0 + V;       // source of the element right of my vector
+    const int z_lo = (tz == 0) ? p.nz - 1 : z0 - 1;   // source of the element left of my vector
+    const int z_hi = (tz == p.ntz - 1) ? 0 : z0 + V;  // source of the element right of my vector
     T f[Q][V];
+    const S* pl = f0;
     static_for<Q>([&](auto lc) {
         XLB_IDX(l, lc);
         using D = Dir<Q, l>;
-        const int xs = D::cx == 0 ? x : (D::cx == 1 ? xm : xp);
-        const int ys = D::cy == 0 ? y : (D::cy == 1 ? ym : yp);
-        const S* row = f0 + l * p.qs + ((long long)xs * p.ny + ys) * p.nz;
+        const long long ox = D::cx == 0 ? ox0 : (D::cx == 1 ? oxm : oxp);
+        const int oy = D::cy == 0 ? oy0 : (D::cy == 1 ? oym : oyp);
+        const S* row = pl + (ox + oy);
         const Vec<S, V> v = ld_vec<S, V>(row + z0);
         if (D::cz == 0) {
 #pragma unroll
             for (int j = 0; j < V; ++j) f[l][j] = to_compute<T, S>(v.v[j]);
         } else if (D::cz == 1) {  // pull from z-1
-            S left = shfl_up1(v.v[V - 1]);
-            if (edge_lo) left = row[z_lo];
+            const S left = ld_if(row + z_lo, edge_lo, shfl_up1(v.v[V - 1]));
             f[l][0] = to_compute<T, S>(left);
 #pragma unroll
             for (int j = 1; j < V; ++j) f[l][j] = to_compute<T, S>(v.v[j - 1]);
         } else {  // pull from z+1
-            S right = shfl_down1(v.v[0]);
-            if (edge_hi) right = row[z_hi];
+            const S right = ld_if(row + z_hi, edge_hi, shfl_down1(v.v[0]));
 #pragma unroll
             for (int j = 0; j < V - 1; ++j) f[l][j] = to_compute<T, S>(v.v[j + 1]);
             f[l][V - 1] = to_compute<T, S>(right);
         }
+        pl += p.qs;
     });
     if (!active) return;
 
@@ -210,12 +235,14 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_c
         collide_column<T, Q, COLL, V, j>(f, omega, HAS_BC && k_full[j]);
     });
     // ---- one aligned vector store per population
+    S* ql = f1 + cell;
 #pragma unroll
     for (int l = 0; l < Q; ++l) {
         Vec<S, V> o;
 #pragma unroll
         for (int j = 0; j < V; ++j) o.v[j] = to_store<S, T>(f[l][j]);
-        st_vec<S, V>(f1 + l * p.qs + cell, o);
+        st_vec<S, V>(ql, o);
+        ql += p.qs;
     }
 }
 

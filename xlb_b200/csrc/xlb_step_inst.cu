@@ -23,6 +23,9 @@ static int launch_vector(const StepParams& p0, cudaStream_t st) {
     constexpr int BLOCK = XLB_TUNE_BLOCK;
     StepParams p = p0;
     p.ntz = p.nz / V;
+    p.ntz_shift = -1;
+    for (int b = 0; b < 31; ++b)
+        if ((1 << b) == p.ntz) p.ntz_shift = b;
     const long long nvec = (long long)p.ny * p.ntz;
     dim3 grid((unsigned)((nvec + BLOCK - 1) / BLOCK), (unsigned)(p.x_end - p.x_begin), 1);
     step_vector_kernel<T, S, Q, COLL, V, BLOCK, XLB_TUNE_MINB, HAS_BC><<<grid, BLOCK, 0, st>>>(p);

@@ -1,1 +1,1 @@
-from .distribute import distribute as distribute, SlabDecomposition as SlabDecomposition
+from .distribute import distribute as distribute, SlabDecomposition as SlabDecomposition, HaloExchange as HaloExchange, DistributedStepper as DistributedStepper

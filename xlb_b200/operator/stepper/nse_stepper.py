@@ -114,8 +114,10 @@ class IncompressibleNavierStokesStepper(Stepper):
         return self._plan
 
     # ------------------------------------------------------------------ the step
-    @Operator.register_backend(ComputeBackend.CUDA)
-    def cuda_implementation(self, f_0, f_1, bc_mask, missing_mask, omega, timestep):
+    def launch_range(self, f_0, f_1, bc_mask, missing_mask, omega, timestep, x_begin, x_end):
+        """One ``xlb_step`` launch that updates planes ``[x_begin, x_end)`` of ``f_1`` (local plane indices, ghost
+        planes included in the numbering).  The multi-GPU schedule (xlb_b200/distribute) issues the two edge
+        planes and the interior as separate launches of this method."""
         q = self.velocity_set.q
         if f_0.dtype != self.store_dtype or f_1.dtype != self.store_dtype:
             raise ValueError(f"populations must be stored as {self.store_dtype} under policy {self.precision_policy.name}")
@@ -123,14 +125,19 @@ class IncompressibleNavierStokesStepper(Stepper):
         self._check_field(f_1, "f_1", q)
         if f_0.shape != f_1.shape:
             raise ValueError("f_0 and f_1 must have the same shape")
-        _, dom, table, n_bc, x_begin, x_end = self._get_plan(f_0)
+        _, dom, table, n_bc, _, _ = self._get_plan(f_0)
         if n_bc:
             self._check_field(bc_mask, "bc_mask", 1)
             self._check_field(missing_mask, "missing_mask", q)
         rc = lib().xlb_step(
             byref(dom), self.collision.abi_model, f_0.data_ptr(), f_1.data_ptr(),
             bc_mask.data_ptr() if n_bc else None, missing_mask.data_ptr() if n_bc else None, table.data_ptr() if n_bc else None, n_bc,
-            float(omega), int(timestep), x_begin, x_end, self.kernel_variant, stream_ptr(),
+            float(omega), int(timestep), int(x_begin), int(x_end), self.kernel_variant, stream_ptr(),
         )
         check(rc, "IncompressibleNavierStokesStepper")
+
+    @Operator.register_backend(ComputeBackend.CUDA)
+    def cuda_implementation(self, f_0, f_1, bc_mask, missing_mask, omega, timestep):
+        _, _, _, _, x_begin, x_end = self._get_plan(f_0)
+        self.launch_range(f_0, f_1, bc_mask, missing_mask, omega, timestep, x_begin, x_end)
         return f_0, f_1
