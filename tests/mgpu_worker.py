@@ -1,0 +1,71 @@
+"""torchrun worker: N-rank x-slab run == single-GPU run of the same global problem, bitwise.
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P tests/mgpu_worker.py
+"""
+
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+
+def main():
+    from oracle import cases
+    from tests.util import build_product, to_dev
+    from xlb_b200.distribute import SlabDecomposition, distribute
+
+    rank = int(os.environ["RANK"])
+    local_rank = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local_rank)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    world = dist.get_world_size()
+    todo = [
+        (cases.cavity3d(0, shape=(8 * world, 12, 16), omega=1.7), 25),
+        (cases.sphere3d((12 * world if world > 2 else 36, 24, 24)), 25),
+        (cases.cavity3d(0, shape=(6 * world + 1, 10, 8), lattice="D3Q27", collision="KBC", omega=1.8, policy="FP64FP64"), 10),  # uneven slabs
+        (cases.cavity3d(0, shape=(4 * world, 16, 16), policy="FP32FP16", omega=1.5), 10),
+    ]
+    for case, nsteps in todo:
+        for overlap in (True, False):
+            # single-GPU reference of the global problem, on every rank
+            st, _ = build_product(case)
+            f_0, f_1, bc_mask, missing = st.prepare_fields()
+            f_0 = to_dev(cases.random_state(case, seed=3))
+            for i in range(nsteps):
+                f_0, f_1 = st(f_0, f_1, bc_mask, missing, case["omega"], i)
+                f_0, f_1 = f_1, f_0
+            ref, ref_bc, ref_mm = f_0.clone(), bc_mask.clone(), missing.clone()
+            # distributed run
+            dec = SlabDecomposition()
+            st, _ = build_product(case, decomposition=dec)
+            dst = distribute(st, st.grid, st.velocity_set, overlap=overlap)
+            g_0, g_1, g_bc, g_mm = dst.prepare_fields()
+            x0, n = dec.local_range(case["shape"][0])
+            assert torch.equal(dst.owned(g_bc), ref_bc[:, x0 : x0 + n]), "bc_mask slab differs"
+            assert torch.equal(dst.owned(g_mm), ref_mm[:, x0 : x0 + n]), "missing_mask slab differs"
+            init = to_dev(cases.random_state(case, seed=3))
+            g_0[:, 1:-1] = init[:, x0 : x0 + n]
+            dst.halo.exchange(g_0)
+            for i in range(nsteps):
+                g_0, g_1 = dst(g_0, g_1, g_bc, g_mm, case["omega"], i)
+                g_0, g_1 = g_1, g_0
+            torch.cuda.synchronize()
+            same = torch.equal(dst.owned(g_0), ref[:, x0 : x0 + n])
+            full = dst.gather(g_0)
+            same_all = torch.equal(full, ref)
+            if not (same and same_all):
+                d = (dst.owned(g_0).double() - ref[:, x0 : x0 + n].double()).abs().max().item()
+                raise AssertionError(f"rank {rank}: {case['name']} overlap={overlap}: distributed != single GPU (max abs diff {d:.3e})")
+            if rank == 0:
+                print(f"OK {case['name']} world={world} overlap={overlap} steps={nsteps}: bitwise equal to the single-GPU run", flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

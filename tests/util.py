@@ -33,11 +33,15 @@ def init_xlb(lattice, policy):
     return vs, pol
 
 
-def build_product(case, backend_config=None):
-    """-> (stepper, [bc objects]) with ids 1.. in list order (registry reset so ids match the oracle's)."""
+def build_product(case, backend_config=None, decomposition=None):
+    """-> (stepper, [bc objects]) with ids 1.. in list order (registry reset so ids match the oracle's).
+    ``decomposition`` (a SlabDecomposition) builds the stepper on this rank's x-slab of the case."""
     init_xlb(case["lattice"], case["policy"])
     boundary_condition_registry.next_id = 1
-    grid = grid_factory(case["shape"], compute_backend=ComputeBackend.CUDA)
+    if decomposition is not None:
+        grid = decomposition.make_grid(case["shape"])
+    else:
+        grid = grid_factory(case["shape"], compute_backend=ComputeBackend.CUDA)
     bcs = []
     for spec in case["bcs"]:
         kind = spec["kind"]

@@ -33,9 +33,9 @@ def build(instance, variants):
         print("built", path)
 
 
-def run(workload, steps):
+def run(workload, steps, only=""):
     rows = []
-    for lib in sorted(glob.glob(os.path.join(SWEEP_DIR, "lib_*.so"))):
+    for lib in sorted(glob.glob(os.path.join(SWEEP_DIR, f"lib_{only}*.so"))):
         env = dict(os.environ, XLB_B200_LIB=lib)
         r = subprocess.run(
             [sys.executable, os.path.join(ROOT, "bench.py"), "--workload", workload, "--steps", str(steps), "--warmup", "3", "--no-e2e", "--no-cpu-baseline"],
@@ -59,4 +59,5 @@ if __name__ == "__main__":
         steps = 20
         if "--steps" in sys.argv:
             steps = int(sys.argv[sys.argv.index("--steps") + 1])
-        run(sys.argv[2], steps)
+        only = sys.argv[sys.argv.index("--only") + 1] if "--only" in sys.argv else ""
+        run(sys.argv[2], steps, only)

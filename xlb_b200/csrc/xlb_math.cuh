@@ -115,43 +115,123 @@ XLB_D T kbc_delta_s(const T (&pi)[6]) {
     }
 }
 
-// ---------------------------------------------------------------------------- fused-kernel arithmetic
-// The fused step evaluates the same formulas as the reference but shares work between a direction L
-// and its opposite O (c_O = -c_L, w_O = w_L):
-//     feq_L = rw*(1 - usqr) + rw*cu + 0.5*rw*cu^2,   feq_O = rw*(1 - usqr) - rw*cu + 0.5*rw*cu^2,   rw = rho*w_L
-// and u = (sum c f) * (1/rho).  This differs from quadratic_equilibrium.py:25-30 / first_moment.py:16-18 only
-// in rounding (a few ulp of the compute type) -- the same freedom XLA takes when it fuses and contracts the
-// JAX expression -- and is covered by the parity tolerances (1e-6 one step / 1e-5 N steps FP32, 1e-13 / 1e-12 FP64).
-XLB_D float fast_div(float a, float b) { return __fdividef(a, b); }  // MUFU.RCP * a, <= 2 ulp
-XLB_D double fast_div(double a, double b) { return a / b; }
-XLB_D float rcp_of(float x) { return __frcp_rn(x); }
-XLB_D double rcp_of(double x) { return 1.0 / x; }
-
-template <typename T, int Q, int V, int J>
-XLB_D void moments_fused(const T (&f)[Q][V], T& rho, T (&u)[3]) {
-    T r = T(0), sx = T(0), sy = T(0), sz = T(0);
-    bool f0 = true, fx = true, fy = true, fz = true;
-    static_for<Q>([&](auto lc) {
-        XLB_IDX(l, lc);
-        using D = Dir<Q, l>;
-        const T v = f[l][J];
-        acc_signed<1>(r, f0, v);
-        acc_signed<D::cx>(sx, fx, v);
-        acc_signed<D::cy>(sy, fy, v);
-        acc_signed<D::cz>(sz, fz, v);
-    });
-    rho = r;
-    const T inv = rcp_of(r);
-    u[0] = (axis0<Q>() > 0) ? T(0) : sx * inv;
-    u[1] = sy * inv;
-    u[2] = sz * inv;
+// signed index into the distinct delta_s values used by collide_cols: 0 -> delta_s = 0, +k -> ds[k], -k -> -ds[k]
+template <int Q, int L>
+XLB_HD constexpr int kbc_ds_index() {
+    if (Q == 27) {
+        switch (L) {
+            case 9: case 18: return 1;
+            case 3: case 6: return 2;
+            case 1: case 2: return 3;
+            case 12: case 24: return 4;
+            case 21: case 15: return -4;
+            case 10: case 20: return 5;
+            case 19: case 11: return -5;
+            case 8: case 4: return 6;
+            case 7: case 5: return -6;
+            default: return 0;
+        }
+    } else if (Q == 9) {
+        switch (L) {
+            case 3: case 6: return 1;
+            case 1: case 2: return -1;
+            case 8: case 7: return 2;
+            case 4: case 5: return -2;
+            default: return 0;
+        }
+    }
+    return 0;
 }
 
+// ---------------------------------------------------------------------------- fused-kernel arithmetic
+// The fused step evaluates the reference's formulas with work shared between a direction L and its opposite O
+// (c_O = -c_L, w_O = w_L):
+//     feq_L = even + odd, feq_O = even - odd,  even = rw*(1 - usqr) + 0.5*rw*cu^2,  odd = rw*cu,  rw = rho*w_L, cu = 3 c_L.u
+//     BGK :  f - omega*(f - feq)           = (1-omega)*f + omega*feq
+//     KBC :  f - beta*(2 ds + gamma*dh)     = (1 - beta*gamma)*f + beta*gamma*feq - beta*(2-gamma)*ds
+// and u = (sum c f)*(1/rho).  This differs from quadratic_equilibrium.py:25-30 / bgk.py:29-32 / kbc.py:70-79 only in
+// rounding (a few ulp of the compute type) -- the freedom XLA takes when it fuses the JAX expression -- and is covered
+// by the parity tolerances.  The translation units are compiled with -fmad=false and every multiply-add below is an
+// explicit fma, so all kernel variants (vector / scalar / generic) produce bit-identical results.
+//
+// Number types: the arithmetic is written once over N = double, float, or F2 = two FP32 cells packed in a 64-bit
+// register pair.  F2 maps onto Blackwell's packed FP32 pipe (SASS FADD2 / FMUL2 / FFMA2, sm_100+), which halves the
+// number of issue slots of the FP32 collision.
+struct F2 {
+    float2 v;
+};
+XLB_D F2 operator+(F2 a, F2 b) { return {__fadd2_rn(a.v, b.v)}; }
+XLB_D F2 operator-(F2 a) { return {make_float2(-a.v.x, -a.v.y)}; }
+XLB_D F2 operator-(F2 a, F2 b) { return {__fadd2_rn(a.v, make_float2(-b.v.x, -b.v.y))}; }
+XLB_D F2 operator*(F2 a, F2 b) { return {__fmul2_rn(a.v, b.v)}; }
+XLB_D F2 fma_(F2 a, F2 b, F2 c) { return {__ffma2_rn(a.v, b.v, c.v)}; }
+XLB_D float fma_(float a, float b, float c) { return fmaf(a, b, c); }
+XLB_D double fma_(double a, double b, double c) { return fma(a, b, c); }
+
+template <typename N>
+struct Num {
+    using scalar = N;
+    static constexpr int lanes = 1;
+};
+template <>
+struct Num<F2> {
+    using scalar = float;
+    static constexpr int lanes = 2;
+};
+template <typename N>
+XLB_D N splat(typename Num<N>::scalar s) { return s; }
+template <>
+XLB_D F2 splat<F2>(float s) { return {make_float2(s, s)}; }
+
+XLB_D float fast_div(float a, float b) { return __fdividef(a, b); }  // MUFU.RCP * a, <= 2 ulp
+XLB_D double fast_div(double a, double b) { return a / b; }
+XLB_D F2 fast_div(F2 a, F2 b) { return {make_float2(__fdividef(a.v.x, b.v.x), __fdividef(a.v.y, b.v.y))}; }
+XLB_D float rcp_of(float x) { return __frcp_rn(x); }
+XLB_D double rcp_of(double x) { return 1.0 / x; }
+XLB_D F2 rcp_of(F2 x) { return {make_float2(__frcp_rn(x.v.x), __frcp_rn(x.v.y))}; }
+// lane-wise select: flag[k] ? a : b
+XLB_D float pick(const bool* flag, float a, float b) { return flag[0] ? a : b; }
+XLB_D double pick(const bool* flag, double a, double b) { return flag[0] ? a : b; }
+XLB_D F2 pick(const bool* flag, F2 a, F2 b) { return {make_float2(flag[0] ? a.v.x : b.v.x, flag[1] ? a.v.y : b.v.y)}; }
+
+// columns J .. J+lanes-1 of f[l] as one number, and back
+template <typename N, typename T, int Q, int V>
+XLB_D N col_get(const T (&f)[Q][V], int l, int J) {
+    if constexpr (Num<N>::lanes == 2) {
+        return N{make_float2(f[l][J], f[l][J + 1])};
+    } else {
+        return f[l][J];
+    }
+}
+template <typename N, typename T, int Q, int V>
+XLB_D void col_set(T (&f)[Q][V], int l, int J, N x) {
+    if constexpr (Num<N>::lanes == 2) {
+        f[l][J] = x.v.x;
+        f[l][J + 1] = x.v.y;
+    } else {
+        f[l][J] = x;
+    }
+}
+
+// weight class of direction L (0 rest, 1 axis, 2 face diagonal, 3 cube diagonal)
+template <int Q, int L>
+XLB_HD constexpr int wclass() {
+    return (Lat<Q>::c(L, 0) != 0) + (Lat<Q>::c(L, 1) != 0) + (Lat<Q>::c(L, 2) != 0);
+}
+template <int Q>
+XLB_HD constexpr double wclass_weight(int k) {
+    for (int l = 0; l < Q; ++l)
+        if ((Lat<Q>::c(l, 0) != 0) + (Lat<Q>::c(l, 1) != 0) + (Lat<Q>::c(l, 2) != 0) == k) return Lat<Q>::w(l);
+    return 0.0;
+}
+template <int Q>
+XLB_HD constexpr int n_wclass() { return Q == 27 ? 4 : 3; }
+
 // cu = 3 c_L.u from the pre-scaled velocity u3 = 3u
-template <typename T, int Q, int L>
-XLB_D T cu_of(const T (&u3)[3]) {
+template <typename N, int Q, int L>
+XLB_D N cu_of(const N (&u3)[3]) {
     using D = Dir<Q, L>;
-    T s = T(0);
+    N s = u3[2];
     bool first = true;
     acc_signed<D::cx>(s, first, u3[0]);
     acc_signed<D::cy>(s, first, u3[1]);
@@ -159,96 +239,207 @@ XLB_D T cu_of(const T (&u3)[3]) {
     return s;
 }
 
-// symmetric (even in c) and antisymmetric parts of feq for the pair (L, opp L); base = 1 - usqr
-template <typename T, int Q, int L>
-XLB_D void feq_pair(T rho, const T (&u3)[3], T base, T& even, T& odd) {
-    const T rw = rho * T(Dir<Q, L>::w);
-    const T cu = cu_of<T, Q, L>(u3);
-    even = rw * (T(0.5) * cu * cu + base);
-    odd = rw * cu;
+// scaled equilibrium of the pair (L, opp L): even = k*feq_even, odd = k*feq_odd where the scale k is folded into
+// the per-weight-class constants a = k*rho*w, ah = 0.5*a, ab = a*(1 - usqr)
+template <typename N, int Q, int L>
+XLB_D void feq_pair(const N (&u3)[3], const N* a, const N* ah, const N* ab, N& even, N& odd) {
+    constexpr int k = wclass<Q, L>();
+    const N cu = cu_of<N, Q, L>(u3);
+    even = fma_(ah[k] * cu, cu, ab[k]);
+    odd = a[k] * cu;
 }
 
-// Collide column J in place.  If fullway is set the COLLISION-step FullwayBounceBackBC result
-// f_post[l] = f_post_stream[opp l] (bc_fullway_bounce_back.py:50-56) is selected instead.
-template <typename T, int Q, int COLL, int V, int J>
-XLB_D void collide_column(T (&f)[Q][V], T omega, bool fullway) {
-    T rho, u[3];
-    moments_fused<T, Q, V, J>(f, rho, u);
-    const T base = T(1.0) - usqr_of<T>(u, axis0<Q>());
-    const T u3[3] = {T(3.0) * u[0], T(3.0) * u[1], T(3.0) * u[2]};
+template <typename N, typename S, int Q>
+XLB_D void wclass_constants(N rho, N base, N scale, N* a, N* ah, N* ab) {
+#pragma unroll
+    for (int k = 0; k < n_wclass<Q>(); ++k) {
+        a[k] = (scale * rho) * splat<N>(static_cast<S>(wclass_weight<Q>(k)));
+        ah[k] = splat<N>(S(0.5)) * a[k];
+        ab[k] = a[k] * base;
+    }
+}
+
+// Collide columns J .. J+lanes-1 in place.  fullway[k] selects the COLLISION-step FullwayBounceBackBC result
+// f_post[l] = f_post_stream[opp l] (bc_fullway_bounce_back.py:50-56) for lane k: the populations are swapped with
+// their opposites up front and the relaxation is switched off for that lane (omega = 0, rho = 1, 1/rho = 0 keep
+// every intermediate finite), so the fast path carries no per-direction select.
+template <typename N, typename T, int Q, int COLL, int V, int J>
+XLB_D void collide_cols(T (&f)[Q][V], T omega_s, const bool* fullway, bool any_fullway) {
+    using S = typename Num<N>::scalar;
+    constexpr int LN = Num<N>::lanes;
+    if (any_fullway) {
+#pragma unroll
+        for (int k = 0; k < LN; ++k) {
+            if (fullway[k]) {
+                static_for<Q>([&](auto lc) {
+                    XLB_IDX(l, lc);
+                    constexpr int o = Dir<Q, l>::o;
+                    if (o > l) {
+                        const T t = f[l][J + k];
+                        f[l][J + k] = f[o][J + k];
+                        f[o][J + k] = t;
+                    }
+                });
+            }
+        }
+    }
+    // ---- moments (zero_moment.py:14-17, first_moment.py:14-18)
+    N rho = splat<N>(S(0)), sx = rho, sy = rho, sz = rho;
+    bool b0 = true, bx = true, by = true, bz = true;
+    static_for<Q>([&](auto lc) {
+        XLB_IDX(l, lc);
+        using D = Dir<Q, l>;
+        const N v = col_get<N>(f, l, J);
+        acc_signed<1>(rho, b0, v);
+        acc_signed<D::cx>(sx, bx, v);
+        acc_signed<D::cy>(sy, by, v);
+        acc_signed<D::cz>(sz, bz, v);
+    });
+    N inv = rcp_of(rho);
+    N omega = splat<N>(static_cast<S>(omega_s));
+    if (any_fullway) {
+        rho = pick(fullway, splat<N>(S(1)), rho);
+        inv = pick(fullway, splat<N>(S(0)), inv);
+        omega = pick(fullway, splat<N>(S(0)), omega);
+    }
+    N u3[3];
+    const N three_inv = splat<N>(S(3)) * inv;
+    u3[0] = (axis0<Q>() > 0) ? splat<N>(S(0)) : sx * three_inv;
+    u3[1] = sy * three_inv;
+    u3[2] = sz * three_inv;
+    // base = 1 - usqr = 1 - 1.5 u.u = 1 - (u3.u3)/6
+    N uu = u3[2] * u3[2];
+    uu = fma_(u3[1], u3[1], uu);
+    if (axis0<Q>() == 0) uu = fma_(u3[0], u3[0], uu);
+    const N base = fma_(splat<N>(S(-1.0 / 6.0)), uu, splat<N>(S(1)));
+    N a[4], ah[4], ab[4];
     if (COLL == XLB_BGK) {
+        // out = (1-omega) f + omega feq, with omega folded into the class constants
+        wclass_constants<N, S, Q>(rho, base, omega, a, ah, ab);
+        const N keep = splat<N>(S(1)) - omega;
         static_for<Q>([&](auto lc) {
             XLB_IDX(l, lc);
             constexpr int o = Dir<Q, l>::o;
-            if (o == l) {  // rest population: cu = 0
-                const T fl = f[l][J];
-                const T nl = fl - omega * (fl - rho * T(Dir<Q, l>::w) * base);
-                f[l][J] = fullway ? fl : nl;
+            if (o == l) {
+                col_set<N>(f, l, J, fma_(keep, col_get<N>(f, l, J), ab[0]));
             } else if (o > l) {
-                T even, odd;
-                feq_pair<T, Q, l>(rho, u3, base, even, odd);
-                const T fl = f[l][J], fo = f[o][J];
-                const T nl = fl - omega * (fl - (even + odd));
-                const T no = fo - omega * (fo - (even - odd));
-                f[l][J] = fullway ? fo : nl;
-                f[o][J] = fullway ? fl : no;
+                N even, odd;
+                feq_pair<N, Q, l>(u3, a, ah, ab, even, odd);
+                col_set<N>(f, l, J, fma_(keep, col_get<N>(f, l, J), even + odd));
+                col_set<N>(f, o, J, fma_(keep, col_get<N>(f, o, J), even - odd));
             }
         });
     } else {
         // ---- KBC (kbc.py:40-79).  Pi = sum cc fneq only sees the even part of fneq; delta_s is even too.
-        T pi[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
+        wclass_constants<N, S, Q>(rho, base, splat<N>(S(1)), a, ah, ab);
+        N pi[6];
+#pragma unroll
+        for (int k = 0; k < 6; ++k) pi[k] = splat<N>(S(0));
         static_for<Q>([&](auto lc) {
             XLB_IDX(l, lc);
             constexpr int o = Dir<Q, l>::o;
             if (o > l) {
-                T even, odd;
-                feq_pair<T, Q, l>(rho, u3, base, even, odd);
-                acc_second_moment<Q, l>(pi, (f[l][J] + f[o][J]) - T(2.0) * even);
+                N even, odd;
+                feq_pair<N, Q, l>(u3, a, ah, ab, even, odd);
+                const N e2 = fma_(splat<N>(S(-2)), even, col_get<N>(f, l, J) + col_get<N>(f, o, J));
+                acc_second_moment<Q, l>(pi, e2);
             }
         });
-        const T beta = T(0.5) * omega;
-        const T inv_beta = T(1.0) / beta;
-        T sp1 = T(0), sp2 = T(0);
+        // the distinct values of delta_s (kbc.py:96-174); index 0 = directions with delta_s = 0
+        N ds[7];
+        ds[0] = splat<N>(S(0));
+        if (Q == 27) {
+            const N Nxz = pi[0] - pi[5], Nyz = pi[3] - pi[5];
+            const N sixth = splat<N>(S(1.0 / 6.0)), quarter = splat<N>(S(0.25));
+            ds[1] = (splat<N>(S(2)) * Nxz - Nyz) * sixth;   // l = 9, 18   (+-x)
+            ds[2] = (splat<N>(S(2)) * Nyz - Nxz) * sixth;   // l = 3, 6    (+-y)
+            ds[3] = -(Nxz + Nyz) * sixth;                    // l = 1, 2    (+-z)
+            ds[4] = pi[1] * quarter;                         // xy: + for (12, 24), - for (21, 15)
+            ds[5] = pi[2] * quarter;                         // xz: + for (10, 20), - for (19, 11)
+            ds[6] = pi[4] * quarter;                         // yz: + for (8, 4),   - for (7, 5)
+        } else {  // D2Q9 (kernel axes y, z): delta_s = shear / 4
+            const N quarter = splat<N>(S(0.25));
+            ds[1] = (pi[3] - pi[5]) * quarter;               // l = 3, 6 (+), l = 1, 2 (-)
+            ds[2] = pi[4] * quarter;                         // l = 8, 7 (+), l = 4, 5 (-)
+            ds[3] = ds[4] = ds[5] = ds[6] = splat<N>(S(0));
+        }
+        auto ds_of = [&](auto lc) -> N {
+            XLB_IDX(l, lc);
+            constexpr int idx = kbc_ds_index<Q, l>();
+            if constexpr (idx == 0) {
+                return ds[0];
+            } else if constexpr (idx > 0) {
+                return ds[idx];
+            } else {
+                return -ds[-idx];
+            }
+        };
+        const N beta = splat<N>(S(0.5)) * omega;
+        const N inv_beta = rcp_of(splat<N>(S(0.5)) * splat<N>(static_cast<S>(omega_s)));
+        N sp1 = splat<N>(S(0)), sp2 = splat<N>(S(0));
         static_for<Q>([&](auto lc) {
             XLB_IDX(l, lc);
             constexpr int o = Dir<Q, l>::o;
             if (o == l) {
-                const T fe = rho * T(Dir<Q, l>::w) * base;
-                const T dh = f[l][J] - fe;  // delta_s of the rest direction is 0
-                sp2 += fast_div(dh, fe) * dh;
+                const N fe = ab[0];
+                const N dh = col_get<N>(f, l, J) - fe;  // delta_s of the rest direction is 0
+                sp2 = fma_(fast_div(dh, fe), dh, sp2);
             } else if (o > l) {
-                T even, odd;
-                feq_pair<T, Q, l>(rho, u3, base, even, odd);
-                const T ds = kbc_delta_s<T, Q, l>(pi);
-                const T fel = even + odd, feo = even - odd;
-                const T dhl = (f[l][J] - fel) - ds, dho = (f[o][J] - feo) - ds;
-                const T tl = fast_div(dhl, fel), to = fast_div(dho, feo);
-                sp1 += (tl + to) * ds;
-                sp2 += tl * dhl + to * dho;
+                N even, odd;
+                feq_pair<N, Q, l>(u3, a, ah, ab, even, odd);
+                const N fel = even + odd, feo = even - odd;
+                N dhl = col_get<N>(f, l, J) - fel, dho = col_get<N>(f, o, J) - feo;
+                if constexpr (kbc_ds_index<Q, l>() != 0) {
+                    const N d = ds_of(lc);
+                    dhl = dhl - d;
+                    dho = dho - d;
+                    const N tl = fast_div(dhl, fel), to = fast_div(dho, feo);
+                    sp1 = fma_(tl + to, d, sp1);
+                    sp2 = fma_(tl, dhl, sp2);
+                    sp2 = fma_(to, dho, sp2);
+                } else {
+                    sp2 = fma_(fast_div(dhl, fel), dhl, sp2);
+                    sp2 = fma_(fast_div(dho, feo), dho, sp2);
+                }
             }
         });
-        const T gamma = inv_beta - (T(2.0) - inv_beta) * fast_div(sp1, T(1e-32) + sp2);
+        const N gamma = inv_beta - (splat<N>(S(2)) - inv_beta) * fast_div(sp1, splat<N>(S(1e-32)) + sp2);
+        // out = A f + B feq - C ds,  A = 1 - beta gamma, B = beta gamma, C = beta (2 - gamma)
+        const N B = beta * gamma;
+        const N A = splat<N>(S(1)) - B;
+        const N C = beta * (splat<N>(S(2)) - gamma);
+        N cds[7];
+#pragma unroll
+        for (int k = 0; k < 7; ++k) cds[k] = C * ds[k];
+#pragma unroll
+        for (int k = 0; k < n_wclass<Q>(); ++k) {  // fold B into the class constants
+            a[k] = B * a[k];
+            ah[k] = B * ah[k];
+            ab[k] = B * ab[k];
+        }
         static_for<Q>([&](auto lc) {
             XLB_IDX(l, lc);
             constexpr int o = Dir<Q, l>::o;
             if (o == l) {
-                const T fl = f[l][J];
-                const T dh = fl - rho * T(Dir<Q, l>::w) * base;
-                const T nl = fl - beta * (gamma * dh);
-                f[l][J] = fullway ? fl : nl;
+                col_set<N>(f, l, J, fma_(A, col_get<N>(f, l, J), ab[0]));
             } else if (o > l) {
-                T even, odd;
-                feq_pair<T, Q, l>(rho, u3, base, even, odd);
-                const T ds = kbc_delta_s<T, Q, l>(pi);
-                const T fl = f[l][J], fo = f[o][J];
-                const T dhl = (fl - (even + odd)) - ds, dho = (fo - (even - odd)) - ds;
-                const T nl = fl - beta * (T(2.0) * ds + gamma * dhl);
-                const T no = fo - beta * (T(2.0) * ds + gamma * dho);
-                f[l][J] = fullway ? fo : nl;
-                f[o][J] = fullway ? fl : no;
+                N even, odd;
+                feq_pair<N, Q, l>(u3, a, ah, ab, even, odd);
+                constexpr int idx = kbc_ds_index<Q, l>();
+                if constexpr (idx > 0) even = even - cds[idx];
+                if constexpr (idx < 0) even = even + cds[-idx];
+                col_set<N>(f, l, J, fma_(A, col_get<N>(f, l, J), even + odd));
+                col_set<N>(f, o, J, fma_(A, col_get<N>(f, o, J), even - odd));
             }
         });
     }
+}
+
+// scalar entry point used by the per-cell generic engine
+template <typename T, int Q, int COLL, int V, int J>
+XLB_D void collide_column(T (&f)[Q][V], T omega, bool fullway) {
+    const bool flags[1] = {fullway};
+    collide_cols<T, T, Q, COLL, V, J>(f, omega, flags, fullway);
 }
 
 // ZouHeBC (bc_zouhe.py:165-304) on one cell: f = post-stream populations (column 0), miss = missing
