@@ -37,6 +37,8 @@ WORKLOADS = {
     "cavity256_d3q19_bgk_fp32": ("D3Q19", "BGK", "FP32FP32", (256, 256, 256), 1.0, "cavity"),
     "sphere384_d3q27_kbc_fp32": ("D3Q27", "KBC", "FP32FP32", (384, 128, 128), 1.6, "sphere"),
     "sphere768_d3q27_kbc_fp32": ("D3Q27", "KBC", "FP32FP32", (768, 256, 256), 1.6, "sphere"),
+    "sphere384x256x512_d3q27_kbc_fp32": ("D3Q27", "KBC", "FP32FP32", (384, 256, 512), 1.6, "sphere"),
+    "cavity768_d3q19_bgk_fp16": ("D3Q19", "BGK", "FP32FP16", (512, 768, 768), 1.0, "cavity"),
     "cavity1024_d3q19_bgk_fp16": ("D3Q19", "BGK", "FP32FP16", (1024, 1024, 1024), 1.0, "cavity"),
     "cavity640_d3q19_bgk_fp16": ("D3Q19", "BGK", "FP32FP16", (640, 640, 640), 1.0, "cavity"),
 }
@@ -110,7 +112,7 @@ class ClockSampler:
 
 
 # --------------------------------------------------------------------------- case construction (product objects)
-def build_case(workload, local_shape=None, slab=None):
+def build_case(workload, slab=None, shape=None, variant=0):
     """Product-side objects of a workload.  BC index sets are generated per slab (global coords) so that the
     1536^3-class cases never materialise a global index list on one rank."""
     import numpy as np
@@ -123,7 +125,8 @@ def build_case(workload, local_shape=None, slab=None):
     from xlb_b200.operator.stepper import IncompressibleNavierStokesStepper
     from xlb_b200.precision_policy import PrecisionPolicy
 
-    lattice, collision, policy, shape, omega, kind = WORKLOADS[workload]
+    lattice, collision, policy, shape0, omega, kind = WORKLOADS[workload]
+    shape = tuple(shape) if shape is not None else shape0
     pol = PrecisionPolicy[policy]
     vs = getattr(xlb.velocity_set, lattice)(precision_policy=pol, compute_backend=ComputeBackend.CUDA)
     xlb.init(velocity_set=vs, default_backend=ComputeBackend.CUDA, default_precision_policy=pol)
@@ -157,7 +160,7 @@ def build_case(workload, local_shape=None, slab=None):
             ExtrapolationOutflowBC(indices=box_ne["right"]),
             HalfwayBounceBackBC(indices=sphere),
         ]
-    stepper = IncompressibleNavierStokesStepper(grid=grid, boundary_conditions=bcs, collision_type=collision)
+    stepper = IncompressibleNavierStokesStepper(grid=grid, boundary_conditions=bcs, collision_type=collision, backend_config={"kernel_variant": variant})
     return stepper, vs, pol, shape, omega
 
 
@@ -252,7 +255,9 @@ def run_native(args):
 
     workload = args.workload
     lattice, collision, policy, shape, omega, kind = WORKLOADS[workload]
-    stepper, vs, pol, shape, omega = build_case(workload, slab=slab)
+    if world > 1 and not args.strong:
+        shape = (shape[0] * world,) + tuple(shape[1:])  # weak scaling: the N=1 block per GPU, stacked along x
+    stepper, vs, pol, shape, omega = build_case(workload, slab=slab, shape=shape, variant=args.variant)
     if slab is not None:
         from xlb_b200.distribute import distribute
 
@@ -317,7 +322,7 @@ def run_native(args):
         achieved = bytes_per_launch / (k_ms * 1e-3) / 1e9
         roofline = {
             "bound": "hbm",
-            "kernel": "step_vector_kernel",
+            "kernel": {0: "xlb_step (auto variant)", 2: "step_vector_kernel", 3: "step_generic_kernel", 4: "step_bulk_kernel"}.get(args.variant, "xlb_step"),
             "achieved": achieved,
             "peak": peak,
             "unit": "GB/s",
@@ -347,7 +352,7 @@ def run_native(args):
         "warmup": max(args.warmup, 3),
         "ms_per_step": ms / args.steps,
         "higher_is_better": True,
-        "scaling": "strong" if world > 1 else "weak",
+        "scaling": "strong" if (world > 1 and args.strong) else "weak",
         "vs_baseline": None,
         "dtype": DTYPE_NAME[policy],
         "data": "synthetic",
@@ -364,6 +369,7 @@ def run_native(args):
         line["roofline"] = roofline
     if e2e:
         line["e2e"] = e2e
+        line["e2e_resident_api"] = run_resident_api(stepper, f_0, f_1, bc_mask, missing, omega, t, ncell, min(args.steps, 20))
     if world == 1 and not args.no_cpu_baseline:
         base = cpu_baseline(workload)
         line["cpu_baseline"] = {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")}
@@ -373,41 +379,63 @@ def run_native(args):
     return 0
 
 
-def run_e2e(stepper, f_0, f_1, bc_mask, missing, omega, t, ncell, steps):
-    """Same metric with HOST buffers: every step copies the populations pinned-host -> device, runs the step and
-    copies the result device -> pinned-host (masks / BC tables are static and stay resident)."""
+def run_e2e(stepper, f_0, f_1, bc_mask, missing, omega, t, ncell, steps, chunk_planes=32):
+    """Same metric with HOST buffers through the public host-facing API (``HostStreamedStepper``): every step moves the
+    populations pinned-host -> device, runs ``xlb_step`` and moves the result device -> pinned-host, as an x-chunk
+    pipeline over three streams (masks / BC tables are static and stay resident).  A device->host read of one
+    result element closes each step."""
     import torch
+
+    from xlb_b200.operator.stepper import HostStreamedStepper
 
     h_in = torch.empty(f_0.shape, dtype=f_0.dtype, pin_memory=True)
     h_out = torch.empty(f_1.shape, dtype=f_1.dtype, pin_memory=True)
     h_in.copy_(f_0)
     torch.cuda.synchronize()
+    hs = HostStreamedStepper(stepper, chunk_planes=chunk_planes)
     ev0 = torch.cuda.Event(enable_timing=True)
     ev1 = torch.cuda.Event(enable_timing=True)
-    # one untimed pass
-    f_0.copy_(h_in, non_blocking=True)
-    stepper(f_0, f_1, bc_mask, missing, omega, t)
-    h_out.copy_(f_1, non_blocking=True)
+    h_in, h_out = hs(h_in, h_out, bc_mask, missing, omega, t)  # one untimed pass
+    h_in, h_out = h_out, h_in
     torch.cuda.synchronize()
     ev0.record()
+    probe = 0.0
     for i in range(steps):
-        f_0.copy_(h_in, non_blocking=True)
-        stepper(f_0, f_1, bc_mask, missing, omega, t + 1 + i)
-        h_out.copy_(f_1, non_blocking=True)
+        h_in, h_out = hs(h_in, h_out, bc_mask, missing, omega, t + 1 + i)
         h_in, h_out = h_out, h_in
+        torch.cuda.current_stream().synchronize()
+        probe += float(h_in[0, 0, 0, 0])  # the step's result is on the host
     ev1.record()
     torch.cuda.synchronize()
     ms = ev0.elapsed_time(ev1)
     nbytes = f_0.numel() * f_0.element_size()
+    halo = 2 * len(hs._state["chunks"]) * f_0.shape[0] * f_0.shape[2] * f_0.shape[3] * f_0.element_size()
     return {
         "value": ncell * steps / (ms * 1e-3) / 1e6,
         "unit": UNIT,
-        "h2d_bytes_per_step": int(nbytes),
+        "h2d_bytes_per_step": int(nbytes + halo),
         "d2h_bytes_per_step": int(nbytes),
         "steps": steps,
         "ms_per_step": ms / steps,
-        "note": "populations pinned-host -> device, xlb_step, device -> pinned-host every step",
+        "note": f"HostStreamedStepper: pinned-host populations, {len(hs._state['chunks'])} x-chunks of {hs._state['P']} planes pipelined over h2d / compute / d2h streams; finite={probe == probe}",
     }
+
+
+def run_resident_api(stepper, f_0, f_1, bc_mask, missing, omega, t, ncell, steps):
+    """The call a user of the reference API makes (device-resident fields, ``stepper(...)`` + swap in a Python loop),
+    with the per-step scalars going host -> device and one result element read back device -> host every step."""
+    import torch
+
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    probe = 0.0
+    for i in range(steps):
+        f_0, f_1 = stepper(f_0, f_1, bc_mask, missing, omega, t + i)
+        f_0, f_1 = f_1, f_0
+        probe += float(f_0[0, 0, 0, 0])  # blocking 4-byte read of this step's result
+    dt = time.perf_counter() - t0
+    return {"value": ncell * steps / dt / 1e6, "unit": UNIT, "steps": steps, "ms_per_step": dt / steps * 1e3,
+            "note": "device-resident fields through the Python API, blocking D2H read of one result element per step (wall clock)"}
 
 
 def main():
@@ -421,10 +449,13 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-overlap", action="store_true")
+    ap.add_argument("--variant", type=int, default=0, help="kernel variant of xlb_step (0 auto, 2 vector, 3 generic, 4 bulk-staged)")
+    ap.add_argument("--strong", action="store_true", help="N>1: keep the global shape of the workload (strong scaling) instead of one block per GPU")
     args = ap.parse_args()
     if args.workload is None:
-        # N=1: BASELINE configs[1] (512^3 D3Q19 BGK FP32FP32).  N>1: configs[3] (1024^3 FP32FP16, strong scaling).
-        args.workload = "cavity512_d3q19_bgk_fp32" if args.gpus == 1 else "cavity1024_d3q19_bgk_fp16"
+        # BASELINE configs[1] (512^3 D3Q19 BGK FP32FP32) per GPU; N>1 stacks N such blocks along x (weak scaling).
+        # BASELINE configs[3] is `--workload cavity1024_d3q19_bgk_fp16 --strong`.
+        args.workload = "cavity512_d3q19_bgk_fp32"
     if args.impl == "reference":
         return run_reference(args)
     return run_native(args)

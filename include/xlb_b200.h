@@ -46,7 +46,7 @@ enum {
 /* error codes */
 enum { XLB_EINVAL = -1, XLB_EUNSUPPORTED = -2, XLB_EALIGN = -3 };
 /* kernel variants for xlb_step (0 picks the tuned default) */
-enum { XLB_VARIANT_AUTO = 0, XLB_VARIANT_SCALAR = 1, XLB_VARIANT_VECTOR = 2, XLB_VARIANT_GENERIC = 3 };
+enum { XLB_VARIANT_AUTO = 0, XLB_VARIANT_SCALAR = 1, XLB_VARIANT_VECTOR = 2, XLB_VARIANT_GENERIC = 3, XLB_VARIANT_BULK = 4 };
 
 /* One row per BC id (index = the uint8 stored in bc_mask; row 0 unused).  Built on the host and
  * uploaded once; replaces the per-stepper BC specialisation of nse_stepper.py:351-380. */

@@ -160,3 +160,80 @@ def test_error_paths():
         st(f_0.cpu(), f_1, bc_mask, missing, 1.0, 0)  # host tensor: no CPU path
     with pytest.raises(ValueError):
         st(f_0[:, ::2], f_1[:, ::2], bc_mask, missing, 1.0, 0)  # non-contiguous
+
+
+@pytest.mark.parametrize("case,chunk", [(cases.sphere3d((48, 24, 24)), 7), (cases.cavity3d(0, shape=(21, 12, 16), omega=1.7), 4),
+                                         (cases.periodic((16, 8, 8), lattice="D3Q27", collision="KBC"), 16),
+                                         (cases.cavity3d(16, policy="FP32FP16", omega=1.5), 5)], ids=lambda v: v["name"] if isinstance(v, dict) else str(v))
+def test_host_streamed_step_equals_resident(case, chunk):
+    """HostStreamedStepper (pinned host populations, x-chunk pipeline over three streams) == resident step, bitwise."""
+    from xlb_b200.operator.stepper import HostStreamedStepper
+
+    st, _ = build_product(case)
+    f_0, f_1, bc_mask, missing = st.prepare_fields()
+    f_0 = to_dev(cases.random_state(case, seed=9))
+    h0 = torch.empty(f_0.shape, dtype=f_0.dtype, pin_memory=True)
+    h1 = torch.empty(f_0.shape, dtype=f_0.dtype, pin_memory=True)
+    h0.copy_(f_0)
+    hs = HostStreamedStepper(st, chunk_planes=chunk)
+    for i in range(3):
+        f_0, f_1 = st(f_0, f_1, bc_mask, missing, case["omega"], i)
+        f_0, f_1 = f_1, f_0
+        h0, h1 = hs(h0, h1, bc_mask, missing, case["omega"], i)
+        h0, h1 = h1, h0
+    torch.cuda.synchronize()
+    assert torch.equal(f_0.cpu(), h0)
+    with pytest.raises(ValueError):
+        hs(f_0, f_1, bc_mask, missing, 1.0, 0)
+
+
+BULK_CASES = [
+    cases.cavity3d(0, shape=(5, 6, 256), omega=1.7),
+    cases.cavity3d(0, shape=(4, 5, 512), omega=1.0),
+    cases.cavity3d(0, shape=(4, 4, 256), omega=1.7, policy="FP64FP64"),
+    cases.cavity3d(0, shape=(4, 4, 256), omega=1.7, policy="FP32FP16"),
+    cases.cavity3d(0, shape=(4, 6, 768), lattice="D3Q27", collision="KBC", omega=1.8),
+    cases.sphere3d((28, 16, 256)),
+    cases.sphere3d((24, 16, 256), policy="FP64FP64", inlet="pressure"),
+    cases.periodic((3, 3, 256), lattice="D3Q27", collision="KBC"),
+    cases.cavity2d(0, shape=(20, 256), collision="KBC"),
+]
+
+
+@pytest.mark.parametrize("case", BULK_CASES, ids=lambda c: c["name"])
+def test_bulk_variant(case):
+    """The persistent bulk-copy-staged kernel (cp.async.bulk + mbarrier ring) == the vector kernel bitwise, and within
+    tolerance of the oracle."""
+    got, ref = _one_step(case, _lib.VARIANT_BULK)
+    tol = TOL_ONE_STEP[case["policy"]] * (4 if case["collision"] == "KBC" else 1)
+    assert rel_err(got, ref) <= tol
+    vec, _ = _one_step(case, _lib.VARIANT_VECTOR)
+    assert np.array_equal(got, vec)
+
+
+def test_bulk_variant_rejects_unaligned_shapes():
+    case = cases.cavity3d(0, shape=(4, 4, 24))
+    st, _ = build_product(case, backend_config={"kernel_variant": _lib.VARIANT_BULK})
+    f_0, f_1, bc_mask, missing = st.prepare_fields()
+    with pytest.raises(ValueError):
+        st(f_0, f_1, bc_mask, missing, 1.0, 0)
+
+
+def test_bulk_variant_many_steps_and_slab_ranges():
+    """Multi-tile pipeline (more tiles than resident blocks) over 20 steps, and x sub-range launches."""
+    case = cases.cavity3d(0, shape=(40, 48, 256), omega=1.6)
+    a, _ = build_product(case, backend_config={"kernel_variant": _lib.VARIANT_BULK})
+    f_0, f_1, bc_mask, missing = a.prepare_fields()
+    b, _ = build_product(case, backend_config={"kernel_variant": _lib.VARIANT_VECTOR})
+    g_0, g_1, _, _ = b.prepare_fields()
+    for i in range(20):
+        f_0, f_1 = a(f_0, f_1, bc_mask, missing, case["omega"], i)
+        f_0, f_1 = f_1, f_0
+        g_0, g_1 = b(g_0, g_1, bc_mask, missing, case["omega"], i)
+        g_0, g_1 = g_1, g_0
+    assert torch.equal(f_0, g_0)
+    f_1.zero_()
+    for xb, xe in [(0, 1), (1, 39), (39, 40)]:
+        a.launch_range(f_0, f_1, bc_mask, missing, case["omega"], 0, xb, xe)
+    b(g_0, g_1, bc_mask, missing, case["omega"], 0)
+    assert torch.equal(f_1, g_1)

@@ -33,12 +33,12 @@ def build(instance, variants):
         print("built", path)
 
 
-def run(workload, steps, only=""):
+def run(workload, steps, only="", variant=0):
     rows = []
     for lib in sorted(glob.glob(os.path.join(SWEEP_DIR, f"lib_{only}*.so"))):
         env = dict(os.environ, XLB_B200_LIB=lib)
         r = subprocess.run(
-            [sys.executable, os.path.join(ROOT, "bench.py"), "--workload", workload, "--steps", str(steps), "--warmup", "3", "--no-e2e", "--no-cpu-baseline"],
+            [sys.executable, os.path.join(ROOT, "bench.py"), "--workload", workload, "--steps", str(steps), "--warmup", "3", "--no-e2e", "--no-cpu-baseline", "--variant", str(variant)],
             env=env, capture_output=True, text=True,
         )
         line = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
@@ -60,4 +60,5 @@ if __name__ == "__main__":
         if "--steps" in sys.argv:
             steps = int(sys.argv[sys.argv.index("--steps") + 1])
         only = sys.argv[sys.argv.index("--only") + 1] if "--only" in sys.argv else ""
-        run(sys.argv[2], steps, only)
+        variant = int(sys.argv[sys.argv.index("--variant") + 1]) if "--variant" in sys.argv else 0
+        run(sys.argv[2], steps, only, variant)

@@ -18,7 +18,7 @@ OBJ_DIR = os.path.join(HERE, "_lib", "obj")
 LIB_PATH = os.path.join(OUT_DIR, "libxlb_b200.so")
 
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
-COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-Xptxas", "-v"]
+COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-fmad=false", "-Xptxas", "-v"]
 
 POLICIES = {  # tag -> (compute type, store type)
     "f32f32": ("float", "float"),

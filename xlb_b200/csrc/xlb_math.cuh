@@ -80,8 +80,8 @@ XLB_D void acc_second_moment(T (&pi)[6], T v) {
     constexpr int cc[6] = {D::cx * D::cx, D::cx * D::cy, D::cx * D::cz, D::cy * D::cy, D::cy * D::cz, D::cz * D::cz};
 #pragma unroll
     for (int k = 0; k < 6; ++k) {
-        if (cc[k] == 1) pi[k] += v;
-        if (cc[k] == -1) pi[k] -= v;
+        if (cc[k] == 1) pi[k] = pi[k] + v;
+        if (cc[k] == -1) pi[k] = pi[k] - v;
     }
 }
 
@@ -146,7 +146,7 @@ XLB_HD constexpr int kbc_ds_index() {
 // ---------------------------------------------------------------------------- fused-kernel arithmetic
 // The fused step evaluates the reference's formulas with work shared between a direction L and its opposite O
 // (c_O = -c_L, w_O = w_L):
-//     feq_L = even + odd, feq_O = even - odd,  even = rw*(1 - usqr) + 0.5*rw*cu^2,  odd = rw*cu,  rw = rho*w_L, cu = 3 c_L.u
+//     feq_L = even + odd, feq_O = even - odd,  odd = rw*cu,  even = rw*(1 - usqr) + 0.5*odd*cu,  rw = rho*w_L, cu = 3 c_L.u
 //     BGK :  f - omega*(f - feq)           = (1-omega)*f + omega*feq
 //     KBC :  f - beta*(2 ds + gamma*dh)     = (1 - beta*gamma)*f + beta*gamma*feq - beta*(2-gamma)*ds
 // and u = (sum c f)*(1/rho).  This differs from quadratic_equilibrium.py:25-30 / bgk.py:29-32 / kbc.py:70-79 only in
@@ -242,21 +242,23 @@ XLB_D N cu_of(const N (&u3)[3]) {
 // scaled equilibrium of the pair (L, opp L): even = k*feq_even, odd = k*feq_odd where the scale k is folded into
 // the per-weight-class constants a = k*rho*w, ah = 0.5*a, ab = a*(1 - usqr)
 template <typename N, int Q, int L>
-XLB_D void feq_pair(const N (&u3)[3], const N* a, const N* ah, const N* ab, N& even, N& odd) {
+XLB_D void feq_pair(const N (&u3)[3], const N* a, const N* ab, N& even, N& odd) {
+    using S = typename Num<N>::scalar;
     constexpr int k = wclass<Q, L>();
     const N cu = cu_of<N, Q, L>(u3);
-    even = fma_(ah[k] * cu, cu, ab[k]);
     odd = a[k] * cu;
+    even = fma_(splat<N>(S(0.5)) * odd, cu, ab[k]);
 }
 
 template <typename N, typename S, int Q>
-XLB_D void wclass_constants(N rho, N base, N scale, N* a, N* ah, N* ab) {
-#pragma unroll
-    for (int k = 0; k < n_wclass<Q>(); ++k) {
-        a[k] = (scale * rho) * splat<N>(static_cast<S>(wclass_weight<Q>(k)));
-        ah[k] = splat<N>(S(0.5)) * a[k];
+XLB_D void wclass_constants(N rho, N base, N scale, N* a, N* ab) {
+    const N sr = scale * rho;
+    static_for<n_wclass<Q>()>([&](auto kc) {
+        XLB_IDX(k, kc);
+        constexpr double w = wclass_weight<Q>(k);  // forced compile-time evaluation
+        a[k] = sr * splat<N>(static_cast<S>(w));
         ab[k] = a[k] * base;
-    }
+    });
 }
 
 // Collide columns J .. J+lanes-1 in place.  fullway[k] selects the COLLISION-step FullwayBounceBackBC result
@@ -312,10 +314,10 @@ XLB_D void collide_cols(T (&f)[Q][V], T omega_s, const bool* fullway, bool any_f
     uu = fma_(u3[1], u3[1], uu);
     if (axis0<Q>() == 0) uu = fma_(u3[0], u3[0], uu);
     const N base = fma_(splat<N>(S(-1.0 / 6.0)), uu, splat<N>(S(1)));
-    N a[4], ah[4], ab[4];
+    N a[4], ab[4];
     if (COLL == XLB_BGK) {
         // out = (1-omega) f + omega feq, with omega folded into the class constants
-        wclass_constants<N, S, Q>(rho, base, omega, a, ah, ab);
+        wclass_constants<N, S, Q>(rho, base, omega, a, ab);
         const N keep = splat<N>(S(1)) - omega;
         static_for<Q>([&](auto lc) {
             XLB_IDX(l, lc);
@@ -324,14 +326,14 @@ XLB_D void collide_cols(T (&f)[Q][V], T omega_s, const bool* fullway, bool any_f
                 col_set<N>(f, l, J, fma_(keep, col_get<N>(f, l, J), ab[0]));
             } else if (o > l) {
                 N even, odd;
-                feq_pair<N, Q, l>(u3, a, ah, ab, even, odd);
+                feq_pair<N, Q, l>(u3, a, ab, even, odd);
                 col_set<N>(f, l, J, fma_(keep, col_get<N>(f, l, J), even + odd));
                 col_set<N>(f, o, J, fma_(keep, col_get<N>(f, o, J), even - odd));
             }
         });
     } else {
         // ---- KBC (kbc.py:40-79).  Pi = sum cc fneq only sees the even part of fneq; delta_s is even too.
-        wclass_constants<N, S, Q>(rho, base, splat<N>(S(1)), a, ah, ab);
+        wclass_constants<N, S, Q>(rho, base, splat<N>(S(1)), a, ab);
         N pi[6];
 #pragma unroll
         for (int k = 0; k < 6; ++k) pi[k] = splat<N>(S(0));
@@ -340,7 +342,7 @@ XLB_D void collide_cols(T (&f)[Q][V], T omega_s, const bool* fullway, bool any_f
             constexpr int o = Dir<Q, l>::o;
             if (o > l) {
                 N even, odd;
-                feq_pair<N, Q, l>(u3, a, ah, ab, even, odd);
+                feq_pair<N, Q, l>(u3, a, ab, even, odd);
                 const N e2 = fma_(splat<N>(S(-2)), even, col_get<N>(f, l, J) + col_get<N>(f, o, J));
                 acc_second_moment<Q, l>(pi, e2);
             }
@@ -386,7 +388,7 @@ XLB_D void collide_cols(T (&f)[Q][V], T omega_s, const bool* fullway, bool any_f
                 sp2 = fma_(fast_div(dh, fe), dh, sp2);
             } else if (o > l) {
                 N even, odd;
-                feq_pair<N, Q, l>(u3, a, ah, ab, even, odd);
+                feq_pair<N, Q, l>(u3, a, ab, even, odd);
                 const N fel = even + odd, feo = even - odd;
                 N dhl = col_get<N>(f, l, J) - fel, dho = col_get<N>(f, o, J) - feo;
                 if constexpr (kbc_ds_index<Q, l>() != 0) {
@@ -408,13 +410,9 @@ XLB_D void collide_cols(T (&f)[Q][V], T omega_s, const bool* fullway, bool any_f
         const N B = beta * gamma;
         const N A = splat<N>(S(1)) - B;
         const N C = beta * (splat<N>(S(2)) - gamma);
-        N cds[7];
-#pragma unroll
-        for (int k = 0; k < 7; ++k) cds[k] = C * ds[k];
 #pragma unroll
         for (int k = 0; k < n_wclass<Q>(); ++k) {  // fold B into the class constants
             a[k] = B * a[k];
-            ah[k] = B * ah[k];
             ab[k] = B * ab[k];
         }
         static_for<Q>([&](auto lc) {
@@ -424,10 +422,10 @@ XLB_D void collide_cols(T (&f)[Q][V], T omega_s, const bool* fullway, bool any_f
                 col_set<N>(f, l, J, fma_(A, col_get<N>(f, l, J), ab[0]));
             } else if (o > l) {
                 N even, odd;
-                feq_pair<N, Q, l>(u3, a, ah, ab, even, odd);
+                feq_pair<N, Q, l>(u3, a, ab, even, odd);
                 constexpr int idx = kbc_ds_index<Q, l>();
-                if constexpr (idx > 0) even = even - cds[idx];
-                if constexpr (idx < 0) even = even + cds[-idx];
+                if constexpr (idx > 0) even = fma_(-C, ds[idx], even);
+                if constexpr (idx < 0) even = fma_(C, ds[-idx], even);
                 col_set<N>(f, l, J, fma_(A, col_get<N>(f, l, J), even + odd));
                 col_set<N>(f, o, J, fma_(A, col_get<N>(f, o, J), even - odd));
             }

@@ -14,6 +14,11 @@
 #pragma once
 #include "xlb_math.cuh"
 
+// 1: FP32 collision on the packed pipe (two cells per FFMA2 / FADD2 / FMUL2); 0: scalar FP32
+#ifndef XLB_TUNE_PACKED
+#define XLB_TUNE_PACKED 1
+#endif
+
 namespace xlb {
 
 XLB_D int wrap1(int v, int n) { return v < 0 ? v + n : (v >= n ? v - n : v); }
@@ -229,11 +234,18 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_c
         }
     }
     const T omega = static_cast<T>(p.omega);
-    // ---- collide each of my cells in place
-    static_for<V>([&](auto jc) {
-        XLB_IDX(j, jc);
-        collide_column<T, Q, COLL, V, j>(f, omega, HAS_BC && k_full[j]);
-    });
+    // ---- collide my cells in place; FP32 runs two cells per instruction on the packed FP32 pipe (FFMA2 / FADD2 / FMUL2)
+    if constexpr (XLB_TUNE_PACKED && std::is_same<T, float>::value && (V % 2 == 0)) {
+        static_for<V / 2>([&](auto jc) {
+            XLB_IDX(jp, jc);
+            collide_cols<F2, T, Q, COLL, V, 2 * jp>(f, omega, &k_full[2 * jp], HAS_BC && (k_full[2 * jp] || k_full[2 * jp + 1]));
+        });
+    } else {
+        static_for<V>([&](auto jc) {
+            XLB_IDX(j, jc);
+            collide_cols<T, T, Q, COLL, V, j>(f, omega, &k_full[j], HAS_BC && k_full[j]);
+        });
+    }
     // ---- one aligned vector store per population
     S* ql = f1 + cell;
 #pragma unroll

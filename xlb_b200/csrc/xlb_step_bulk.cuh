@@ -1,0 +1,216 @@
+// xlb_step_bulk.cuh -- the fused step as a persistent, bulk-copy-staged pipeline (K1b).
+//
+// Same per-cell arithmetic as step_vector_kernel (xlb_step.cuh), different data movement: the q source rows of a
+// tile (TZ = NT*C consecutive z cells of one (x, y) row) are fetched by the copy engine with 1-D bulk async copies
+// (PTX cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes, SASS UBLKCP) into a STAGES-deep ring of
+// shared-memory buffers, completion is signalled on an mbarrier per stage, and the block prefetches the tiles it
+// will process next while it collides the current one.  What this buys over per-thread LDG:
+//   * DRAM latency is hidden by the prefetch ring instead of by occupancy, so the register-hungry collisions
+//     (D3Q27 KBC, FP16 storage) no longer stall on their own loads;
+//   * no per-thread address arithmetic, shuffles or edge loads for the q pulled populations: lane l of warp 0 issues
+//     the copy of population l (one row base + one 16-byte halo chunk where c_z != 0);
+//   * the +-1 z shift of the pull is a shared-memory index offset; every thread owns C cells NT apart, so all
+//     shared-memory reads are conflict-free 32-bit accesses and all global stores are fully coalesced.
+// Requirements (checked on the host, otherwise the vector kernel runs): nz % TZ == 0, 16-byte aligned rows.
+#pragma once
+#include "xlb_step.cuh"
+
+namespace xlb {
+
+XLB_D uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+
+XLB_D void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+XLB_D void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+XLB_D void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+XLB_D void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "XLB_WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra XLB_DONE_%=;\n\t"
+        "bra XLB_WAIT_%=;\n\t"
+        "XLB_DONE_%=:\n\t}" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+// global -> shared bulk copy, bytes % 16 == 0, both addresses 16-byte aligned; completes on `bar`
+XLB_D void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)), "l"(src), "r"(bytes),
+                 "r"(smem_u32(bar))
+                 : "memory");
+}
+
+template <typename S, int Q, int TZ, bool HAS_BC>
+struct BulkLayout {
+    static constexpr int HE = 16 / (int)sizeof(S);        // halo chunk, elements
+    static constexpr int ROW = TZ + 2 * HE;               // elements per staged population row
+    static constexpr int POP_BYTES = Q * ROW * (int)sizeof(S);
+    static constexpr int MASK_BYTES = HAS_BC ? TZ : 0;
+    static constexpr int STAGE_BYTES = ((POP_BYTES + MASK_BYTES + 127) / 128) * 128;
+    XLB_HD static constexpr int n_shifted() {
+        int n = 0;
+        for (int l = 0; l < Q; ++l) n += Lat<Q>::c(l, 2) != 0;
+        return n;
+    }
+    static constexpr uint32_t TX_BYTES = Q * TZ * sizeof(S) + n_shifted() * 16 + MASK_BYTES;
+    static size_t smem_bytes(int stages) { return (size_t)stages * STAGE_BYTES + 64; }
+};
+
+template <typename T, typename S, int Q, int COLL, int C, int NT, int STAGES, int MINB, bool HAS_BC>
+__global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_constant__ StepParams p) {
+    constexpr int TZ = NT * C;
+    using L = BulkLayout<S, Q, TZ, HAS_BC>;
+    constexpr int HE = L::HE;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + (size_t)STAGES * L::STAGE_BYTES);
+    const S* __restrict__ f0 = static_cast<const S*>(p.f0);
+    S* __restrict__ f1 = static_cast<S*>(p.f1);
+    const int tid = threadIdx.x;
+    const int lane = tid & 31;
+    const int nseg = p.nz / TZ;
+    const int tiles_per_plane = p.ny * nseg;
+    const long long total = (long long)(p.x_end - p.x_begin) * tiles_per_plane;
+    const long long plane = (long long)p.ny * p.nz;
+
+    // lattice vector of the population this lane issues copies for (warp 0 only)
+    int lcx = 0, lcy = 0, lcz = 0;
+    static_for<Q>([&](auto lc) {
+        XLB_IDX(l, lc);
+        if (lane == l) {
+            lcx = Dir<Q, l>::cx;
+            lcy = Dir<Q, l>::cy;
+            lcz = Dir<Q, l>::cz;
+        }
+    });
+
+    auto tile_coords = [&](long long t, int& x, int& y, int& z0) {
+        const int xr = (int)(t / tiles_per_plane);
+        const int r = (int)(t - (long long)xr * tiles_per_plane);
+        y = r / nseg;
+        z0 = (r - y * nseg) * TZ;
+        x = p.x_begin + xr;
+    };
+    // warp 0: fetch tile t into stage s
+    auto issue = [&](long long t, int s) {
+        if (t >= total) return;
+        int x, y, z0;
+        tile_coords(t, x, y, z0);
+        unsigned char* stage = smem_raw + (size_t)s * L::STAGE_BYTES;
+        if (lane == 0) mbar_arrive_expect_tx(&full[s], L::TX_BYTES);
+        __syncwarp();
+        if (lane < Q) {
+            int xs = x - lcx;
+            if (p.x_periodic) xs = wrap1(xs, p.nx);
+            const int ys = wrap1(y - lcy, p.ny);
+            const S* row = f0 + lane * p.qs + (xs * plane + (long long)ys * p.nz);
+            S* dst = reinterpret_cast<S*>(stage) + lane * L::ROW;
+            bulk_g2s(dst + HE, row + z0, TZ * sizeof(S), &full[s]);
+            if (lcz == 1) {  // pull from z-1: the chunk left of the segment (periodic)
+                const int zs = (z0 == 0) ? p.nz - HE : z0 - HE;
+                bulk_g2s(dst, row + zs, 16, &full[s]);
+            } else if (lcz == -1) {  // pull from z+1: the chunk right of the segment (periodic)
+                const int zs = (z0 + TZ == p.nz) ? 0 : z0 + TZ;
+                bulk_g2s(dst + HE + TZ, row + zs, 16, &full[s]);
+            }
+        } else if (HAS_BC && lane == Q) {
+            bulk_g2s(stage + L::POP_BYTES, p.bc_mask + (x * plane + (long long)y * p.nz + z0), TZ, &full[s]);
+        }
+    };
+
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) mbar_init(&full[s], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    if (tid < 32) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) issue((long long)blockIdx.x + (long long)s * gridDim.x, s);
+    }
+
+    const T omega = static_cast<T>(p.omega);
+    int it = 0;
+    for (long long t = blockIdx.x; t < total; t += gridDim.x, ++it) {
+        const int s = it % STAGES;
+        const uint32_t parity = (uint32_t)(it / STAGES) & 1u;
+        int x, y, z0;
+        tile_coords(t, x, y, z0);
+        const unsigned char* stage = smem_raw + (size_t)s * L::STAGE_BYTES;
+        const S* pops = reinterpret_cast<const S*>(stage);
+        mbar_wait(&full[s], parity);
+        // ---- staged rows -> registers (pull shift = index offset)
+        T f[Q][C];
+        static_for<Q>([&](auto lc) {
+            XLB_IDX(l, lc);
+            constexpr int cz = Dir<Q, l>::cz;
+#pragma unroll
+            for (int j = 0; j < C; ++j) f[l][j] = to_compute<T, S>(pops[l * L::ROW + HE + tid + j * NT - cz]);
+        });
+        uint8_t ids[C];
+        bool any_bc = false;
+        if (HAS_BC) {
+#pragma unroll
+            for (int j = 0; j < C; ++j) {
+                ids[j] = stage[L::POP_BYTES + tid + j * NT];
+                any_bc |= ids[j] != 0;
+            }
+        }
+        __syncthreads();  // every thread has consumed stage s
+        if (tid < 32) issue(t + (long long)STAGES * gridDim.x, s);
+
+        bool slow = false;
+        bool k_full[C], k_eq[C];
+#pragma unroll
+        for (int j = 0; j < C; ++j) k_full[j] = k_eq[j] = false;
+        if (HAS_BC && any_bc) {
+#pragma unroll
+            for (int j = 0; j < C; ++j) {
+                if (ids[j]) {
+                    const int k = p.bct[ids[j]].kind;
+                    k_full[j] = k == XLB_BC_FULLWAY;
+                    k_eq[j] = k == XLB_BC_EQUILIBRIUM;
+                    slow |= bc_is_complex(k);
+                }
+            }
+        }
+        const int zc = z0 + tid;
+        if (HAS_BC && slow) {
+            for (int j = 0; j < C; ++j) cell_update_generic<T, S, Q, COLL>(p, x, y, zc + j * NT);
+            continue;
+        }
+        if (HAS_BC && any_bc) {
+#pragma unroll
+            for (int j = 0; j < C; ++j) {
+                if (k_eq[j]) {
+                    const double* tab = p.bct[ids[j]].table;
+#pragma unroll
+                    for (int l = 0; l < Q; ++l) f[l][j] = static_cast<T>(tab[l]);
+                }
+            }
+        }
+        if constexpr (XLB_TUNE_PACKED && std::is_same<T, float>::value && (C % 2 == 0)) {
+            static_for<C / 2>([&](auto jc) {
+                XLB_IDX(jp, jc);
+                collide_cols<F2, T, Q, COLL, C, 2 * jp>(f, omega, &k_full[2 * jp], HAS_BC && (k_full[2 * jp] || k_full[2 * jp + 1]));
+            });
+        } else {
+            static_for<C>([&](auto jc) {
+                XLB_IDX(j, jc);
+                collide_cols<T, T, Q, COLL, C, j>(f, omega, &k_full[j], HAS_BC && k_full[j]);
+            });
+        }
+        S* ql = f1 + (x * plane + (long long)y * p.nz + zc);
+#pragma unroll
+        for (int l = 0; l < Q; ++l) {
+#pragma unroll
+            for (int j = 0; j < C; ++j) ql[j * NT] = to_store<S, T>(f[l][j]);
+            ql += p.qs;
+        }
+    }
+}
+
+}  // namespace xlb

@@ -3,6 +3,7 @@
 // Exposes   int xlb_step_<tag>(const XlbDomain*, int collision, StepParams, int variant, cudaStream_t)
 #include "xlb_host.cuh"
 #include "xlb_step.cuh"
+#include "xlb_step_bulk.cuh"
 
 #ifndef XLB_Q
 #error "compile with -DXLB_Q -DXLB_TC -DXLB_TS -DXLB_TAG"
@@ -12,9 +13,11 @@
 #ifndef XLB_TUNE_BLOCK
 #define XLB_TUNE_BLOCK 128
 #endif
-#ifndef XLB_TUNE_MINB
-#define XLB_TUNE_MINB 1
-#endif
+// default (V, MINB) per instance from the B200 sweeps recorded in profiles/ (tools/sweep.py)
+template <typename S, int Q>
+constexpr int default_vec() { return sizeof(S) == 8 ? 2 : (Q == 27 ? 2 : 4); }
+template <typename S, int Q>
+constexpr int default_minb() { return sizeof(S) == 8 ? 4 : (Q == 27 ? 4 : 5); }
 
 namespace xlb {
 
@@ -28,8 +31,64 @@ static int launch_vector(const StepParams& p0, cudaStream_t st) {
         if ((1 << b) == p.ntz) p.ntz_shift = b;
     const long long nvec = (long long)p.ny * p.ntz;
     dim3 grid((unsigned)((nvec + BLOCK - 1) / BLOCK), (unsigned)(p.x_end - p.x_begin), 1);
-    step_vector_kernel<T, S, Q, COLL, V, BLOCK, XLB_TUNE_MINB, HAS_BC><<<grid, BLOCK, 0, st>>>(p);
+#ifdef XLB_TUNE_MINB
+    constexpr int MINB = XLB_TUNE_MINB;
+#else
+    constexpr int MINB = (V == 1) ? 4 : default_minb<S, Q>();
+#endif
+    step_vector_kernel<T, S, Q, COLL, V, BLOCK, MINB, HAS_BC><<<grid, BLOCK, 0, st>>>(p);
     return count_launch(cudaGetLastError());
+}
+
+#ifndef XLB_TUNE_STAGES
+#define XLB_TUNE_STAGES 2
+#endif
+#ifndef XLB_TUNE_BMINB
+#define XLB_TUNE_BMINB 1
+#endif
+#ifndef XLB_TUNE_C
+#define XLB_TUNE_C 2
+#endif
+
+// persistent bulk-copy-staged kernel (xlb_step_bulk.cuh); returns -1000 when the shape does not qualify
+template <typename T, typename S, int Q, int COLL, int C, int NT, bool HAS_BC>
+static int launch_bulk(const StepParams& p, cudaStream_t st) {
+    constexpr int TZ = NT * C;
+    constexpr int STAGES = XLB_TUNE_STAGES;
+    using L = BulkLayout<S, Q, TZ, HAS_BC>;
+    auto kern = step_bulk_kernel<T, S, Q, COLL, C, NT, STAGES, XLB_TUNE_BMINB, HAS_BC>;
+    static int blocks_per_sm = 0, n_sm = 0;
+    const size_t smem = L::smem_bytes(STAGES);
+    if (blocks_per_sm == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return count_launch(e);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kern, NT, smem);
+        if (e != cudaSuccess) return count_launch(e);
+        if (blocks_per_sm < 1) blocks_per_sm = 1;
+    }
+    const long long total = (long long)(p.x_end - p.x_begin) * p.ny * (p.nz / TZ);
+    long long grid = (long long)blocks_per_sm * n_sm;
+    if (grid > total) grid = total;
+    kern<<<(unsigned)grid, NT, smem, st>>>(p);
+    return count_launch(cudaGetLastError());
+}
+
+template <typename T, typename S, int Q, int COLL, bool HAS_BC>
+static int try_bulk(const StepParams& p, cudaStream_t st) {
+    constexpr int C = XLB_TUNE_C;
+    const uintptr_t a0 = reinterpret_cast<uintptr_t>(p.f0), am = reinterpret_cast<uintptr_t>(p.bc_mask);
+    const bool aligned = (a0 % 16 == 0) && ((p.qs * sizeof(S)) % 16 == 0) && ((p.nz * sizeof(S)) % 16 == 0) && (!HAS_BC || am % 16 == 0);
+    if (!aligned) return -1000;
+#ifdef XLB_TUNE_NT
+    if (p.nz % (XLB_TUNE_NT * C) == 0) return launch_bulk<T, S, Q, COLL, C, XLB_TUNE_NT, HAS_BC>(p, st);
+#else
+    if (p.nz % (256 * C) == 0) return launch_bulk<T, S, Q, COLL, C, 256, HAS_BC>(p, st);
+    if (p.nz % (128 * C) == 0) return launch_bulk<T, S, Q, COLL, C, 128, HAS_BC>(p, st);
+#endif
+    return -1000;
 }
 
 template <typename T, typename S, int Q, int COLL>
@@ -45,10 +104,15 @@ static int step_coll(const StepParams& p, int variant, cudaStream_t st) {
 #ifdef XLB_TUNE_V
     constexpr int VMAX = XLB_TUNE_V;
 #else
-    constexpr int VMAX = (sizeof(S) == 8) ? 2 : 4;
+    constexpr int VMAX = default_vec<S, Q>();
 #endif
     const bool has_bc = p.bc_mask != nullptr && p.bct != nullptr;
     if (variant == XLB_VARIANT_GENERIC) return launch_generic<T, S, Q, COLL>(p, st);
+    if (variant == XLB_VARIANT_BULK) {
+        const int rc = has_bc ? try_bulk<T, S, Q, COLL, true>(p, st) : try_bulk<T, S, Q, COLL, false>(p, st);
+        if (rc != -1000) return rc;
+        return set_error(XLB_EALIGN, "xlb_step: the bulk variant needs nz to be a multiple of the tile (256 or 512 cells) and 16-byte aligned rows");
+    }
     const uintptr_t a0 = reinterpret_cast<uintptr_t>(p.f0), a1 = reinterpret_cast<uintptr_t>(p.f1);
     const bool vec_ok = (p.nz % VMAX == 0) && (p.qs % VMAX == 0) && (a0 % (VMAX * sizeof(S)) == 0) && (a1 % (VMAX * sizeof(S)) == 0) &&
                         (!has_bc || reinterpret_cast<uintptr_t>(p.bc_mask) % VMAX == 0);

@@ -31,7 +31,8 @@ class Grid:
     def bounding_box_indices(self, shape=None, remove_edges=False):
         """Index lists of the domain faces (grid.py:135-191): 'left'/'right' = x min/max, 'front'/'back' =
         y min/max (3-D), 'bottom'/'top' = last axis min/max.  ``remove_edges`` drops the rim of every face."""
-        shape = tuple(self.shape if shape is None else shape)
+        # on an x-slab grid (xlb_b200.distribute) index lists stay global, like the reference's sharded grids
+        shape = tuple(getattr(self, "global_shape", self.shape) if shape is None else shape)
         dim = len(shape)
         lo = 1 if remove_edges else 0
         rng = [np.arange(lo, n - lo) for n in shape]

@@ -1,2 +1,3 @@
 from .stepper import Stepper as Stepper
 from .nse_stepper import IncompressibleNavierStokesStepper as IncompressibleNavierStokesStepper
+from .host_stepper import HostStreamedStepper as HostStreamedStepper
