@@ -38,6 +38,7 @@ WORKLOADS = {
     "sphere384_d3q27_kbc_fp32": ("D3Q27", "KBC", "FP32FP32", (384, 128, 128), 1.6, "sphere"),
     "sphere768_d3q27_kbc_fp32": ("D3Q27", "KBC", "FP32FP32", (768, 256, 256), 1.6, "sphere"),
     "sphere384x256x512_d3q27_kbc_fp32": ("D3Q27", "KBC", "FP32FP32", (384, 256, 512), 1.6, "sphere"),
+    "cavity384x256x512_d3q27_bgk_fp32": ("D3Q27", "BGK", "FP32FP32", (384, 256, 512), 1.7, "cavity"),
     "cavity768_d3q19_bgk_fp16": ("D3Q19", "BGK", "FP32FP16", (512, 768, 768), 1.0, "cavity"),
     "cavity1024_d3q19_bgk_fp16": ("D3Q19", "BGK", "FP32FP16", (1024, 1024, 1024), 1.0, "cavity"),
     "cavity640_d3q19_bgk_fp16": ("D3Q19", "BGK", "FP32FP16", (640, 640, 640), 1.0, "cavity"),
@@ -441,7 +442,7 @@ def run_resident_api(stepper, f_0, f_1, bc_mask, missing, omega, t, ncell, steps
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS))

@@ -41,7 +41,9 @@ enum {
     XLB_BC_DONOTHING = 4,      /* bc_do_nothing.py:50-54            STREAMING step */
     XLB_BC_ZOUHE_VELOCITY = 5, /* bc_zouhe.py:290-304, bc_type="velocity" */
     XLB_BC_ZOUHE_PRESSURE = 6, /* bc_zouhe.py:290-304, bc_type="pressure" */
-    XLB_BC_EXTRAPOLATION = 7   /* bc_extrapolation_outflow.py:106-145 (streaming apply + post-collision assemble) */
+    XLB_BC_EXTRAPOLATION = 7,  /* bc_extrapolation_outflow.py:106-145 (streaming apply + post-collision assemble) */
+    XLB_BC_REGULARIZED_VELOCITY = 8, /* bc_regularized.py:116-135 (Zou-He + Latt regularisation), bc_type="velocity" */
+    XLB_BC_REGULARIZED_PRESSURE = 9  /* bc_regularized.py:116-135, bc_type="pressure" */
 };
 /* error codes */
 enum { XLB_EINVAL = -1, XLB_EUNSUPPORTED = -2, XLB_EALIGN = -3 };

@@ -235,6 +235,29 @@ class ZouHeBC(BoundaryCondition):
         return np.where(boundary, f_post_bd, f_post).astype(f_post.dtype, copy=False)
 
 
+class RegularizedBC(ZouHeBC):
+    """bc_regularized.py:52-135: Zou-He followed by Latt's regularisation of the boundary populations."""
+
+    # :78-114
+    def regularize_fpop(self, fpop, feq):
+        lat = self.lat
+        weights = lat.w.astype(self.cdt).reshape((-1,) + (1,) * lat.d)  # velocity_set.w is in the compute dtype
+        Qi = lat.qi.astype(self.cdt)
+        f_neq = fpop - feq
+        PiNeq = ops.second_moment(lat, f_neq)
+        QiPi1 = np.tensordot(Qi, PiNeq, axes=(1, 0))
+        fpop1 = 9.0 / 2.0 * weights * QiPi1
+        return feq + fpop1
+
+    # :116-135
+    def __call__(self, f_pre, f_post, bc_mask, missing_mask):
+        boundary = _bmask(self.lat, bc_mask, self.id)
+        feq = self.calculate_equilibrium(f_post, missing_mask)
+        f_post_bd = self.bounceback_nonequilibrium(f_post, feq, missing_mask)
+        f_post_bd = self.regularize_fpop(f_post_bd, feq)
+        return np.where(boundary, f_post_bd, f_post).astype(f_post.dtype, copy=False)
+
+
 class ExtrapolationOutflowBC(BoundaryCondition):
     """bc_extrapolation_outflow.py:48-145 (STREAMING step + post-collision assemble)."""
 

@@ -113,6 +113,15 @@ def sphere3d(
             inlet_bc = dict(kind="ZouHeBC", bc_type="velocity", prescribed_value=(u_max, 0.0, 0.0), indices=box_ne["left"])
     elif inlet == "pressure":
         inlet_bc = dict(kind="ZouHeBC", bc_type="pressure", prescribed_value=1.01, indices=box_ne["left"])
+    elif inlet == "regularized_velocity":  # what examples/cfd/flow_past_sphere_3d.py:107 ships
+        if profile:
+            from .ops import policy_dtypes
+            _, sdt = policy_dtypes(policy)
+            inlet_bc = dict(kind="RegularizedBC", bc_type="velocity", profile_array=poiseuille_profile(shape, u_max, sdt), indices=box_ne["left"])
+        else:
+            inlet_bc = dict(kind="RegularizedBC", bc_type="velocity", prescribed_value=(u_max, 0.0, 0.0), indices=box_ne["left"])
+    elif inlet == "regularized_pressure":
+        inlet_bc = dict(kind="RegularizedBC", bc_type="pressure", prescribed_value=1.01, indices=box_ne["left"])
     else:
         raise ValueError(inlet)
     if outlet == "extrapolation":
@@ -168,12 +177,13 @@ def build_oracle(case):
             b = obc.DoNothingBC(lat, pol, indices=idx, registry=reg)
         elif kind == "ExtrapolationOutflowBC":
             b = obc.ExtrapolationOutflowBC(lat, pol, indices=idx, registry=reg)
-        elif kind == "ZouHeBC":
+        elif kind in ("ZouHeBC", "RegularizedBC"):
+            cls = obc.ZouHeBC if kind == "ZouHeBC" else obc.RegularizedBC
             if "profile_array" in spec:
                 arr = spec["profile_array"]
-                b = obc.ZouHeBC(lat, pol, spec["bc_type"], profile=lambda arr=arr: arr, indices=idx, registry=reg)
+                b = cls(lat, pol, spec["bc_type"], profile=lambda arr=arr: arr, indices=idx, registry=reg)
             else:
-                b = obc.ZouHeBC(lat, pol, spec["bc_type"], prescribed_value=spec["prescribed_value"], indices=idx, registry=reg)
+                b = cls(lat, pol, spec["bc_type"], prescribed_value=spec["prescribed_value"], indices=idx, registry=reg)
         else:
             raise ValueError(kind)
         bcs.append(b)

@@ -41,6 +41,8 @@ def golden_cases():
         (cases.sphere3d((24, 16, 12), lattice="D3Q19", collision="BGK", inlet="pressure", outlet="pressure"), 20),
         (cases.sphere3d((24, 16, 16), outlet="donothing", moving_sphere=(0.01, 0.0, 0.005)), 10),
         (cases.sphere3d((24, 14, 14), policy="FP64FP64", inlet="pressure", outlet="extrapolation"), 10),
+        (cases.sphere3d((28, 16, 16), inlet="regularized_velocity", profile=True), 30),
+        (cases.sphere3d((24, 14, 14), policy="FP64FP64", inlet="regularized_pressure", lattice="D3Q19", collision="BGK"), 20),
     ]
 
 
@@ -50,7 +52,7 @@ def build_reference(case):
     from xlb.compute_backend import ComputeBackend
     from xlb.grid import grid_factory
     from xlb.operator.boundary_condition import (
-        DoNothingBC, EquilibriumBC, ExtrapolationOutflowBC, FullwayBounceBackBC, HalfwayBounceBackBC, ZouHeBC,
+        DoNothingBC, EquilibriumBC, ExtrapolationOutflowBC, FullwayBounceBackBC, HalfwayBounceBackBC, RegularizedBC, ZouHeBC,
     )
     from xlb.operator.boundary_condition.boundary_condition_registry import boundary_condition_registry
     from xlb.operator.stepper import IncompressibleNavierStokesStepper
@@ -78,12 +80,13 @@ def build_reference(case):
             b = DoNothingBC(indices=idx)
         elif kind == "ExtrapolationOutflowBC":
             b = ExtrapolationOutflowBC(indices=idx)
-        elif kind == "ZouHeBC":
+        elif kind in ("ZouHeBC", "RegularizedBC"):
+            ZouHeBC_ = ZouHeBC if kind == "ZouHeBC" else RegularizedBC
             if "profile_array" in spec:
                 arr = spec["profile_array"]
-                b = ZouHeBC(spec["bc_type"], profile=lambda arr=arr: jnp.array(arr), indices=idx)
+                b = ZouHeBC_(spec["bc_type"], profile=lambda arr=arr: jnp.array(arr), indices=idx)
             else:
-                b = ZouHeBC(spec["bc_type"], prescribed_value=spec["prescribed_value"], indices=idx)
+                b = ZouHeBC_(spec["bc_type"], prescribed_value=spec["prescribed_value"], indices=idx)
         else:
             raise ValueError(kind)
         bcs.append(b)

@@ -37,6 +37,9 @@ ONE_STEP = [
     cases.sphere3d((40, 24, 20), lattice="D3Q19", collision="BGK", inlet="pressure", outlet="pressure"),
     cases.sphere3d((36, 24, 24), outlet="donothing", moving_sphere=(0.01, 0.0, 0.005)),
     cases.sphere3d((36, 20, 20), policy="FP64FP64", inlet="pressure", outlet="extrapolation"),
+    cases.sphere3d((48, 24, 24), inlet="regularized_velocity", profile=True),
+    cases.sphere3d((40, 24, 20), inlet="regularized_velocity", policy="FP64FP64"),
+    cases.sphere3d((40, 24, 20), lattice="D3Q19", collision="BGK", inlet="regularized_pressure", outlet="pressure"),
 ]
 VARIANTS = [_lib.VARIANT_AUTO, _lib.VARIANT_SCALAR, _lib.VARIANT_GENERIC]
 
@@ -86,6 +89,7 @@ N_STEP = [
     (cases.sphere3d((48, 24, 24)), 200),
     (cases.sphere3d((48, 24, 24), policy="FP64FP64"), 200),
     (cases.sphere3d((48, 24, 24), profile=True, lattice="D3Q19", collision="BGK", omega=1.5), 100),
+    (cases.sphere3d((48, 24, 24), inlet="regularized_velocity", profile=True), 200),
 ]
 
 

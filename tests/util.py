@@ -15,6 +15,7 @@ from xlb_b200.operator.boundary_condition import (
     ExtrapolationOutflowBC,
     FullwayBounceBackBC,
     HalfwayBounceBackBC,
+    RegularizedBC,
     ZouHeBC,
 )
 from xlb_b200.operator.boundary_condition.boundary_condition_registry import boundary_condition_registry
@@ -56,12 +57,13 @@ def build_product(case, backend_config=None, decomposition=None):
             b = DoNothingBC(indices=idx)
         elif kind == "ExtrapolationOutflowBC":
             b = ExtrapolationOutflowBC(indices=idx)
-        elif kind == "ZouHeBC":
+        elif kind in ("ZouHeBC", "RegularizedBC"):
+            ZouHeBC_ = ZouHeBC if kind == "ZouHeBC" else RegularizedBC
             if "profile_array" in spec:
                 arr = spec["profile_array"]
-                b = ZouHeBC(spec["bc_type"], profile=lambda arr=arr: arr, indices=idx)
+                b = ZouHeBC_(spec["bc_type"], profile=lambda arr=arr: arr, indices=idx)
             else:
-                b = ZouHeBC(spec["bc_type"], prescribed_value=spec["prescribed_value"], indices=idx)
+                b = ZouHeBC_(spec["bc_type"], prescribed_value=spec["prescribed_value"], indices=idx)
         else:
             raise ValueError(kind)
         bcs.append(b)

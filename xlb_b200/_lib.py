@@ -15,6 +15,7 @@ ABI_VERSION = 1
 # enums of include/xlb_b200.h
 BGK, KBC = 0, 1
 BC_NONE, BC_FULLWAY, BC_EQUILIBRIUM, BC_HALFWAY, BC_DONOTHING, BC_ZOUHE_VELOCITY, BC_ZOUHE_PRESSURE, BC_EXTRAPOLATION = range(8)
+BC_REGULARIZED_VELOCITY, BC_REGULARIZED_PRESSURE = 8, 9
 VARIANT_AUTO, VARIANT_SCALAR, VARIANT_VECTOR, VARIANT_GENERIC, VARIANT_BULK = range(5)
 EINVAL, EUNSUPPORTED, EALIGN = -1, -2, -3
 

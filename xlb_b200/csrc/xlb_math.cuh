@@ -183,9 +183,16 @@ XLB_D N splat(typename Num<N>::scalar s) { return s; }
 template <>
 XLB_D F2 splat<F2>(float s) { return {make_float2(s, s)}; }
 
-XLB_D float fast_div(float a, float b) { return __fdividef(a, b); }  // MUFU.RCP * a, <= 2 ulp
+// a / b for b in the normal range (equilibria, entropic sums): one MUFU.RCP + one multiply, <= 2 ulp.  __fdividef would
+// add a range-scaling sequence (FSETP + 2 predicated FMUL) per call that is never needed here.
+XLB_D float rcp_approx(float b) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(b));
+    return r;
+}
+XLB_D float fast_div(float a, float b) { return a * rcp_approx(b); }
 XLB_D double fast_div(double a, double b) { return a / b; }
-XLB_D F2 fast_div(F2 a, F2 b) { return {make_float2(__fdividef(a.v.x, b.v.x), __fdividef(a.v.y, b.v.y))}; }
+XLB_D F2 fast_div(F2 a, F2 b) { return a * F2{make_float2(rcp_approx(b.v.x), rcp_approx(b.v.y))}; }
 XLB_D float rcp_of(float x) { return __frcp_rn(x); }
 XLB_D double rcp_of(double x) { return 1.0 / x; }
 XLB_D F2 rcp_of(F2 x) { return {make_float2(__frcp_rn(x.v.x), __frcp_rn(x.v.y))}; }
@@ -288,15 +295,37 @@ XLB_D void collide_cols(T (&f)[Q][V], T omega_s, const bool* fullway, bool any_f
     // ---- moments (zero_moment.py:14-17, first_moment.py:14-18)
     N rho = splat<N>(S(0)), sx = rho, sy = rho, sz = rho;
     bool b0 = true, bx = true, by = true, bz = true;
-    static_for<Q>([&](auto lc) {
-        XLB_IDX(l, lc);
-        using D = Dir<Q, l>;
-        const N v = col_get<N>(f, l, J);
-        acc_signed<1>(rho, b0, v);
-        acc_signed<D::cx>(sx, bx, v);
-        acc_signed<D::cy>(sy, by, v);
-        acc_signed<D::cz>(sz, bz, v);
-    });
+    N pi[6];  // KBC: sum_l cc_l f_l, accumulated from the pair sums (cc is even in c)
+#pragma unroll
+    for (int k = 0; k < 6; ++k) pi[k] = splat<N>(S(0));
+    if (COLL == XLB_KBC) {
+        static_for<Q>([&](auto lc) {
+            XLB_IDX(l, lc);
+            using D = Dir<Q, l>;
+            constexpr int o = D::o;
+            if (o == l) {
+                acc_signed<1>(rho, b0, col_get<N>(f, l, J));
+            } else if (o > l) {
+                const N fl = col_get<N>(f, l, J), fo = col_get<N>(f, o, J);
+                const N sum = fl + fo, dif = fl - fo;
+                acc_signed<1>(rho, b0, sum);
+                acc_signed<D::cx>(sx, bx, dif);
+                acc_signed<D::cy>(sy, by, dif);
+                acc_signed<D::cz>(sz, bz, dif);
+                acc_second_moment<Q, l>(pi, sum);
+            }
+        });
+    } else {
+        static_for<Q>([&](auto lc) {
+            XLB_IDX(l, lc);
+            using D = Dir<Q, l>;
+            const N v = col_get<N>(f, l, J);
+            acc_signed<1>(rho, b0, v);
+            acc_signed<D::cx>(sx, bx, v);
+            acc_signed<D::cy>(sy, by, v);
+            acc_signed<D::cz>(sz, bz, v);
+        });
+    }
     N inv = rcp_of(rho);
     N omega = splat<N>(static_cast<S>(omega_s));
     if (any_fullway) {
@@ -332,21 +361,19 @@ XLB_D void collide_cols(T (&f)[Q][V], T omega_s, const bool* fullway, bool any_f
             }
         });
     } else {
-        // ---- KBC (kbc.py:40-79).  Pi = sum cc fneq only sees the even part of fneq; delta_s is even too.
+        // ---- KBC (kbc.py:40-79).  Pi_neq = sum cc (f - feq) = sum cc f - rho (u u + I/3): the second moment of the
+        // quadratic equilibrium is exact on D3Q27 / D2Q9, so no pass over feq is needed for it.
         wclass_constants<N, S, Q>(rho, base, splat<N>(S(1)), a, ab);
-        N pi[6];
-#pragma unroll
-        for (int k = 0; k < 6; ++k) pi[k] = splat<N>(S(0));
-        static_for<Q>([&](auto lc) {
-            XLB_IDX(l, lc);
-            constexpr int o = Dir<Q, l>::o;
-            if (o > l) {
-                N even, odd;
-                feq_pair<N, Q, l>(u3, a, ab, even, odd);
-                const N e2 = fma_(splat<N>(S(-2)), even, col_get<N>(f, l, J) + col_get<N>(f, o, J));
-                acc_second_moment<Q, l>(pi, e2);
-            }
-        });
+        {
+            const N r9 = rho * splat<N>(S(1.0 / 9.0));  // u_a u_b = u3_a u3_b / 9
+            const N rx = r9 * u3[0], ry = r9 * u3[1], rz = r9 * u3[2];
+            pi[0] = fma_(-rx, u3[0], pi[0]);  // the isotropic part rho/3 drops out: only differences of the diagonal are used
+            pi[1] = fma_(-rx, u3[1], pi[1]);
+            pi[2] = fma_(-rx, u3[2], pi[2]);
+            pi[3] = fma_(-ry, u3[1], pi[3]);
+            pi[4] = fma_(-ry, u3[2], pi[4]);
+            pi[5] = fma_(-rz, u3[2], pi[5]);
+        }
         // the distinct values of delta_s (kbc.py:96-174); index 0 = directions with delta_s = 0
         N ds[7];
         ds[0] = splat<N>(S(0));
@@ -443,7 +470,7 @@ XLB_D void collide_column(T (&f)[Q][V], T omega, bool fullway) {
 // ZouHeBC (bc_zouhe.py:165-304) on one cell: f = post-stream populations (column 0), miss = missing
 // bits of the cell, e = BC row (prescribed values), velocity type or pressure type.
 template <typename T, int Q>
-XLB_D void zouhe_apply(T (&f)[Q][1], uint32_t miss, const XlbBcEntry& e, bool velocity_type, int x, int y, int z) {
+XLB_D void zouhe_apply(T (&f)[Q][1], uint32_t miss, const XlbBcEntry& e, bool velocity_type, int x, int y, int z, bool regularize = false) {
     int nrm[3] = {0, 0, 0};
     T s_mid = T(0), s_known = T(0);
     static_for<Q>([&](auto lc) {
@@ -488,6 +515,31 @@ XLB_D void zouhe_apply(T (&f)[Q][1], uint32_t miss, const XlbBcEntry& e, bool ve
             f[l][0] = g[o] + feq_dir<T, Q, l>(rho, vel, usqr) - feq_dir<T, Q, o>(rho, vel, usqr);
         }
     });
+    if (regularize) {
+        // RegularizedBC.regularize_fpop (bc_regularized.py:78-114): f = feq + 4.5 w_l (Q_l : Pi_neq),
+        // Pi_neq = sum_l c c (f - feq) (second_moment.py:35-55), Q_l = c c - I/3 with off-diagonals doubled
+        // (velocity_set.py:139-153)
+        T pi[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
+        static_for<Q>([&](auto lc) {
+            XLB_IDX(l, lc);
+            acc_second_moment<Q, l>(pi, f[l][0] - feq_dir<T, Q, l>(rho, vel, usqr));
+        });
+        static_for<Q>([&](auto lc) {
+            XLB_IDX(l, lc);
+            using D = Dir<Q, l>;
+            constexpr int cc[6] = {D::cx * D::cx, D::cx * D::cy, D::cx * D::cz, D::cy * D::cy, D::cy * D::cz, D::cz * D::cz};
+            constexpr bool diag[6] = {true, false, false, true, false, true};
+            T qp = T(0);
+#pragma unroll
+            for (int k = 0; k < 6; ++k) {
+                // components that involve the unused kernel axis of a 2-D lattice vanish (pi = 0 there, cc = 0)
+                if (A0 > 0 && (k == 0 || k == 1 || k == 2)) continue;
+                const T qi = diag[k] ? T(cc[k] - 1.0 / 3.0) : T(2.0 * cc[k]);
+                qp += qi * pi[k];
+            }
+            f[l][0] = feq_dir<T, Q, l>(rho, vel, usqr) + T(4.5) * T(D::w) * qp;
+        });
+    }
 }
 
 }  // namespace xlb

@@ -201,8 +201,8 @@ __global__ void __launch_bounds__(128) apply_bc_kernel(const __grid_constant__ O
             constexpr int o = Dir<Q, l>::o;
             if (miss & (1u << l)) f[l][0] = (kind == XLB_BC_HALFWAY) ? g[o] + static_cast<T>(e.table[l]) : g[o];
         });
-    } else if (kind == XLB_BC_ZOUHE_VELOCITY || kind == XLB_BC_ZOUHE_PRESSURE) {
-        zouhe_apply<T, Q>(f, miss, e, kind == XLB_BC_ZOUHE_VELOCITY, x, y, z);
+    } else if (kind == XLB_BC_ZOUHE_VELOCITY || kind == XLB_BC_ZOUHE_PRESSURE || kind == XLB_BC_REGULARIZED_VELOCITY || kind == XLB_BC_REGULARIZED_PRESSURE) {
+        zouhe_apply<T, Q>(f, miss, e, kind == XLB_BC_ZOUHE_VELOCITY || kind == XLB_BC_REGULARIZED_VELOCITY, x, y, z, kind >= XLB_BC_REGULARIZED_VELOCITY);
     }
 #pragma unroll
     for (int l = 0; l < Q; ++l) st_any<T>(p.o0, p.dt_out, l * p.qs + cell, f[l][0]);

@@ -14,9 +14,12 @@
 #pragma once
 #include "xlb_math.cuh"
 
-// 1: FP32 collision on the packed pipe (two cells per FFMA2 / FADD2 / FMUL2); 0: scalar FP32
-#ifndef XLB_TUNE_PACKED
-#define XLB_TUNE_PACKED 1
+// FP32 collision on the packed pipe (two cells per FFMA2 / FADD2 / FMUL2) or as two independent scalar chains.
+// Measured on B200 (profiles/): packed wins for BGK (issue slots), scalar wins for KBC (instruction-level parallelism).
+#ifdef XLB_TUNE_PACKED
+#define XLB_PACKED(COLL) (XLB_TUNE_PACKED)
+#else
+#define XLB_PACKED(COLL) ((COLL) == XLB_BGK)
 #endif
 
 namespace xlb {
@@ -74,8 +77,8 @@ __device__ __noinline__ void cell_update_generic(const StepParams& p, int x, int
                 f[l][0] = v;
             }
         });
-    } else if (kind == XLB_BC_ZOUHE_VELOCITY || kind == XLB_BC_ZOUHE_PRESSURE) {
-        zouhe_apply<T, Q>(f, miss, *e, kind == XLB_BC_ZOUHE_VELOCITY, x, y, z);
+    } else if (kind == XLB_BC_ZOUHE_VELOCITY || kind == XLB_BC_ZOUHE_PRESSURE || kind == XLB_BC_REGULARIZED_VELOCITY || kind == XLB_BC_REGULARIZED_PRESSURE) {
+        zouhe_apply<T, Q>(f, miss, *e, kind == XLB_BC_ZOUHE_VELOCITY || kind == XLB_BC_REGULARIZED_VELOCITY, x, y, z, kind >= XLB_BC_REGULARIZED_VELOCITY);
     }
     // ---- macroscopic, equilibrium, collision (+ COLLISION-step FullwayBounceBackBC)
     T fps[Q];
@@ -235,7 +238,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_c
     }
     const T omega = static_cast<T>(p.omega);
     // ---- collide my cells in place; FP32 runs two cells per instruction on the packed FP32 pipe (FFMA2 / FADD2 / FMUL2)
-    if constexpr (XLB_TUNE_PACKED && std::is_same<T, float>::value && (V % 2 == 0)) {
+    if constexpr (XLB_PACKED(COLL) && std::is_same<T, float>::value && (V % 2 == 0)) {
         static_for<V / 2>([&](auto jc) {
             XLB_IDX(jp, jc);
             collide_cols<F2, T, Q, COLL, V, 2 * jp>(f, omega, &k_full[2 * jp], HAS_BC && (k_full[2 * jp] || k_full[2 * jp + 1]));

@@ -26,6 +26,13 @@ XLB_D void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster
 XLB_D void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
+// arrival counter of a stage: returns the previous value; acq_rel at CTA scope orders this warp's shared-memory reads of
+// the stage before the refill that the last-arriving warp issues
+XLB_D unsigned stage_arrive(unsigned* cnt) {
+    unsigned old;
+    asm volatile("atom.acq_rel.cta.shared::cta.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(smem_u32(cnt)) : "memory");
+    return old;
+}
 XLB_D void mbar_wait(uint64_t* bar, uint32_t parity) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
@@ -57,7 +64,7 @@ struct BulkLayout {
         return n;
     }
     static constexpr uint32_t TX_BYTES = Q * TZ * sizeof(S) + n_shifted() * 16 + MASK_BYTES;
-    static size_t smem_bytes(int stages) { return (size_t)stages * STAGE_BYTES + 64; }
+    static size_t smem_bytes(int stages) { return (size_t)stages * STAGE_BYTES + 128; }
 };
 
 template <typename T, typename S, int Q, int COLL, int C, int NT, int STAGES, int MINB, bool HAS_BC>
@@ -67,16 +74,18 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
     constexpr int HE = L::HE;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + (size_t)STAGES * L::STAGE_BYTES);
+    unsigned* arrived = reinterpret_cast<unsigned*>(full + STAGES);  // per stage: warps that have consumed it (monotonic)
+    constexpr unsigned NW = NT / 32;
     const S* __restrict__ f0 = static_cast<const S*>(p.f0);
     S* __restrict__ f1 = static_cast<S*>(p.f1);
     const int tid = threadIdx.x;
     const int lane = tid & 31;
     const int nseg = p.nz / TZ;
     const int tiles_per_plane = p.ny * nseg;
-    const long long total = (long long)(p.x_end - p.x_begin) * tiles_per_plane;
+    const int total = (p.x_end - p.x_begin) * tiles_per_plane;  // < 2^31, checked on the host
     const long long plane = (long long)p.ny * p.nz;
 
-    // lattice vector of the population this lane issues copies for (warp 0 only)
+    // lattice vector of the population this lane issues copies for
     int lcx = 0, lcy = 0, lcz = 0;
     static_for<Q>([&](auto lc) {
         XLB_IDX(l, lc);
@@ -87,15 +96,15 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
         }
     });
 
-    auto tile_coords = [&](long long t, int& x, int& y, int& z0) {
-        const int xr = (int)(t / tiles_per_plane);
-        const int r = (int)(t - (long long)xr * tiles_per_plane);
+    auto tile_coords = [&](int t, int& x, int& y, int& z0) {
+        const int xr = t / tiles_per_plane;
+        const int r = t - xr * tiles_per_plane;
         y = r / nseg;
         z0 = (r - y * nseg) * TZ;
         x = p.x_begin + xr;
     };
-    // warp 0: fetch tile t into stage s
-    auto issue = [&](long long t, int s) {
+    // one warp (all 32 lanes): fetch tile t into stage s
+    auto issue = [&](int t, int s) {
         if (t >= total) return;
         int x, y, z0;
         tile_coords(t, x, y, z0);
@@ -123,18 +132,23 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
 
     if (tid == 0) {
 #pragma unroll
-        for (int s = 0; s < STAGES; ++s) mbar_init(&full[s], 1);
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full[s], 1);
+            arrived[s] = 0;
+        }
         mbar_fence_init();
     }
     __syncthreads();
     if (tid < 32) {
 #pragma unroll
-        for (int s = 0; s < STAGES; ++s) issue((long long)blockIdx.x + (long long)s * gridDim.x, s);
+        for (int s = 0; s < STAGES; ++s) {
+            if ((long long)blockIdx.x + (long long)s * gridDim.x < total) issue((int)(blockIdx.x + s * gridDim.x), s);
+        }
     }
 
     const T omega = static_cast<T>(p.omega);
     int it = 0;
-    for (long long t = blockIdx.x; t < total; t += gridDim.x, ++it) {
+    for (int t = blockIdx.x; t < total; t += gridDim.x, ++it) {
         const int s = it % STAGES;
         const uint32_t parity = (uint32_t)(it / STAGES) & 1u;
         int x, y, z0;
@@ -159,8 +173,13 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
                 any_bc |= ids[j] != 0;
             }
         }
-        __syncthreads();  // every thread has consumed stage s
-        if (tid < 32) issue(t + (long long)STAGES * gridDim.x, s);
+        // No block-wide barrier: each warp counts itself off the stage once its reads are done, and the warp that
+        // arrives last refills the stage with the tile STAGES iterations ahead.  Warps never wait for each other.
+        __syncwarp();
+        unsigned prev = 0;
+        if (lane == 0) prev = stage_arrive(&arrived[s]);
+        prev = __shfl_sync(0xffffffffu, prev, 0);
+        if ((prev + 1) % NW == 0 && (long long)t + (long long)STAGES * gridDim.x < total) issue(t + STAGES * (int)gridDim.x, s);
 
         bool slow = false;
         bool k_full[C], k_eq[C];
@@ -192,7 +211,7 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
                 }
             }
         }
-        if constexpr (XLB_TUNE_PACKED && std::is_same<T, float>::value && (C % 2 == 0)) {
+        if constexpr (XLB_PACKED(COLL) && std::is_same<T, float>::value && (C % 2 == 0)) {
             static_for<C / 2>([&](auto jc) {
                 XLB_IDX(jp, jc);
                 collide_cols<F2, T, Q, COLL, C, 2 * jp>(f, omega, &k_full[2 * jp], HAS_BC && (k_full[2 * jp] || k_full[2 * jp + 1]));

@@ -17,7 +17,7 @@
 template <typename S, int Q>
 constexpr int default_vec() { return sizeof(S) == 8 ? 2 : (Q == 27 ? 2 : 4); }
 template <typename S, int Q>
-constexpr int default_minb() { return sizeof(S) == 8 ? 4 : (Q == 27 ? 4 : 5); }
+constexpr int default_minb() { return sizeof(S) == 8 ? 4 : (Q == 27 ? 4 : (sizeof(S) == 2 ? 5 : 4)); }
 
 namespace xlb {
 
@@ -44,7 +44,7 @@ static int launch_vector(const StepParams& p0, cudaStream_t st) {
 #define XLB_TUNE_STAGES 2
 #endif
 #ifndef XLB_TUNE_BMINB
-#define XLB_TUNE_BMINB 1
+#define XLB_TUNE_BMINB 3
 #endif
 #ifndef XLB_TUNE_C
 #define XLB_TUNE_C 2
@@ -70,6 +70,7 @@ static int launch_bulk(const StepParams& p, cudaStream_t st) {
         if (blocks_per_sm < 1) blocks_per_sm = 1;
     }
     const long long total = (long long)(p.x_end - p.x_begin) * p.ny * (p.nz / TZ);
+    if (total >= (1ll << 30)) return -1000;  // tile indices are 32-bit in the kernel
     long long grid = (long long)blocks_per_sm * n_sm;
     if (grid > total) grid = total;
     kern<<<(unsigned)grid, NT, smem, st>>>(p);
@@ -85,7 +86,6 @@ static int try_bulk(const StepParams& p, cudaStream_t st) {
 #ifdef XLB_TUNE_NT
     if (p.nz % (XLB_TUNE_NT * C) == 0) return launch_bulk<T, S, Q, COLL, C, XLB_TUNE_NT, HAS_BC>(p, st);
 #else
-    if (p.nz % (256 * C) == 0) return launch_bulk<T, S, Q, COLL, C, 256, HAS_BC>(p, st);
     if (p.nz % (128 * C) == 0) return launch_bulk<T, S, Q, COLL, C, 128, HAS_BC>(p, st);
 #endif
     return -1000;
@@ -111,12 +111,17 @@ static int step_coll(const StepParams& p, int variant, cudaStream_t st) {
     if (variant == XLB_VARIANT_BULK) {
         const int rc = has_bc ? try_bulk<T, S, Q, COLL, true>(p, st) : try_bulk<T, S, Q, COLL, false>(p, st);
         if (rc != -1000) return rc;
-        return set_error(XLB_EALIGN, "xlb_step: the bulk variant needs nz to be a multiple of the tile (256 or 512 cells) and 16-byte aligned rows");
+        return set_error(XLB_EALIGN, "xlb_step: the bulk variant needs nz to be a multiple of the 256-cell tile and 16-byte aligned rows");
     }
     const uintptr_t a0 = reinterpret_cast<uintptr_t>(p.f0), a1 = reinterpret_cast<uintptr_t>(p.f1);
     const bool vec_ok = (p.nz % VMAX == 0) && (p.qs % VMAX == 0) && (a0 % (VMAX * sizeof(S)) == 0) && (a1 % (VMAX * sizeof(S)) == 0) &&
                         (!has_bc || reinterpret_cast<uintptr_t>(p.bc_mask) % VMAX == 0);
     if (variant == XLB_VARIANT_VECTOR && !vec_ok) return set_error(XLB_EALIGN, "xlb_step: vector variant needs nz, q_stride and base pointers aligned to the vector width");
+    // AUTO: the bulk-staged pipeline where the B200 sweeps show it ahead of the vector kernel (D3Q27 KBC, compute-heavy)
+    if (variant == XLB_VARIANT_AUTO && Q == 27 && COLL == XLB_KBC && sizeof(S) == 4) {
+        const int rc = has_bc ? try_bulk<T, S, Q, COLL, true>(p, st) : try_bulk<T, S, Q, COLL, false>(p, st);
+        if (rc != -1000) return rc;
+    }
     if (vec_ok && variant != XLB_VARIANT_SCALAR) {
         return has_bc ? launch_vector<T, S, Q, COLL, VMAX, true>(p, st) : launch_vector<T, S, Q, COLL, VMAX, false>(p, st);
     }

@@ -8,3 +8,4 @@ from .bc_simple import (
 )
 from .bc_zouhe import ZouHeBC as ZouHeBC
 from .bc_extrapolation_outflow import ExtrapolationOutflowBC as ExtrapolationOutflowBC
+from .bc_regularized import RegularizedBC as RegularizedBC
