@@ -167,37 +167,47 @@ def build_case(workload, slab=None, shape=None, variant=0):
 
 # --------------------------------------------------------------------------- CPU legs (the only users of oracle/)
 def cpu_baseline(workload, budget_s=20.0, max_steps=8):
-    """The NumPy oracle port of the reference's JAX step, timed on this box's host cores on a bounded sample:
-    the same BCs / lattice / policy at 128^3 (BASELINE config 1 when the workload is the cavity)."""
+    """The oracle port of the reference's JAX step (nse_stepper.py:238-282), timed on this box's host cores on a bounded
+    sample: the same BCs / lattice / policy at 128^3 (BASELINE config 1 when the workload is the cavity).  The cavity
+    runs the multi-threaded torch-CPU transcription of the oracle (all host threads, like XLA:CPU would use); the
+    other workloads run the single-threaded NumPy oracle."""
     import numpy as np
+    import torch
 
     from oracle import cases
 
     lattice, collision, policy, shape, omega, kind = WORKLOADS[workload]
-    n = 128 if kind == "cavity" else None
     if kind == "cavity":
-        case = cases.cavity3d(n, policy=policy, lattice=lattice, collision=collision, omega=omega)
+        case = cases.cavity3d(128, policy=policy, lattice=lattice, collision=collision, omega=omega)
     else:
         case = cases.sphere3d((96, 64, 64), policy=policy, lattice=lattice, collision=collision, omega=omega)
     st, _ = cases.build_oracle(case)
     f0, f1, bc, mm = st.prepare_fields()
     f0 = f0.astype(st.sdt)
     ncell = int(np.prod(case["shape"]))
-    f0, f1 = st(f0, f1, bc, mm, omega, 0)  # warm-up (page faults, caches)
+    cores, how = 1, "NumPy oracle, single thread"
+    step = st
+    if kind == "cavity" and collision == "BGK":
+        from oracle.torch_cpu import TorchCavityStepper, to_torch
+
+        step = TorchCavityStepper(st)
+        f0, bc = to_torch(f0), to_torch(bc)
+        cores, how = torch.get_num_threads(), f"torch-CPU transcription of the oracle, {torch.get_num_threads()} threads"
+    f0, f1 = step(f0, f1, bc, mm, omega, 0)  # warm-up (page faults, caches)
     f0, f1 = f1, f0
     t0 = time.perf_counter()
     steps = 0
     while steps < max_steps and (time.perf_counter() - t0) < budget_s:
-        f0, f1 = st(f0, f1, bc, mm, omega, steps + 1)
+        f0, f1 = step(f0, f1, bc, mm, omega, steps + 1)
         f0, f1 = f1, f0
         steps += 1
     dt = time.perf_counter() - t0
     return {
         "value": ncell * steps / dt / 1e6,
         "unit": UNIT,
-        "cores": 1,
+        "cores": cores,
         "kind": "port",
-        "sample": f"{steps} steps of {case['name']} ({ncell} cells), NumPy oracle port of nse_stepper.py:238-282, single thread; host has {os.cpu_count()} cores",
+        "sample": f"{steps} steps of {case['name']} ({ncell} cells), {how}; oracle port of nse_stepper.py:238-282; host has {os.cpu_count()} cores",
         "seconds": dt,
     }
 

@@ -201,6 +201,7 @@ BULK_CASES = [
     cases.sphere3d((24, 16, 256), policy="FP64FP64", inlet="pressure"),
     cases.periodic((3, 3, 256), lattice="D3Q27", collision="KBC"),
     cases.cavity2d(0, shape=(20, 256), collision="KBC"),
+    cases.sphere3d((28, 16, 128)),  # D3Q27 KBC on a 128-wide grid: NT = 64 tiles
 ]
 
 

@@ -132,3 +132,26 @@ def test_fullway_bc(name, shape):
     inside[tuple(np.array(i) for i in idx)] = True
     assert np.all(f[:, ~inside] == 2.0)
     assert np.array_equal(f[:, inside], f_pre[lat.opp_indices][:, inside])
+
+
+@pytest.mark.parametrize("policy,tol", [("FP32FP32", 2e-6), ("FP64FP64", 1e-13)])
+def test_torch_cpu_transcription_matches_oracle(policy, tol):
+    """oracle/torch_cpu.py (the multi-threaded CPU baseline of bench.py) == the NumPy oracle on the benchmark cavity."""
+    import torch
+
+    from oracle import cases
+    from oracle.torch_cpu import TorchCavityStepper, to_torch
+
+    case = cases.cavity3d(12, policy=policy, omega=1.7)
+    ost, _ = cases.build_oracle(case)
+    f0, f1, bc, mm = ost.prepare_fields()
+    f0 = cases.random_state(case, seed=4)
+    ts = TorchCavityStepper(ost)
+    a, b = f0, None
+    ta, bcm = to_torch(f0), to_torch(bc)
+    for i in range(5):
+        _, b = ost(a, None, bc, mm, case["omega"], i)
+        _, tb = ts(ta, None, bcm, None, case["omega"], i)
+        a, ta = b, tb
+    err = np.max(np.abs(ta.numpy().astype(np.float64) - a.astype(np.float64))) / np.max(np.abs(a))
+    assert err <= tol

@@ -14,13 +14,12 @@
 #pragma once
 #include "xlb_math.cuh"
 
-// FP32 collision on the packed pipe (two cells per FFMA2 / FADD2 / FMUL2) or as two independent scalar chains.
-// Measured on B200 (profiles/): packed wins for BGK (issue slots), scalar wins for KBC (instruction-level parallelism).
-#ifdef XLB_TUNE_PACKED
-#define XLB_PACKED(COLL) (XLB_TUNE_PACKED)
-#else
-#define XLB_PACKED(COLL) ((COLL) == XLB_BGK)
+// 1: FP32 collision on the packed pipe (two cells per FFMA2 / FADD2 / FMUL2); 0: two independent scalar chains.
+// Measured on B200 (profiles/*sweep*): packed is ahead for BGK and, once the KBC passes were trimmed, for KBC too.
+#ifndef XLB_TUNE_PACKED
+#define XLB_TUNE_PACKED 1
 #endif
+#define XLB_PACKED(COLL) (XLB_TUNE_PACKED)
 
 namespace xlb {
 

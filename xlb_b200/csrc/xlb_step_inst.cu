@@ -56,7 +56,8 @@ static int launch_bulk(const StepParams& p, cudaStream_t st) {
     constexpr int TZ = NT * C;
     constexpr int STAGES = XLB_TUNE_STAGES;
     using L = BulkLayout<S, Q, TZ, HAS_BC>;
-    auto kern = step_bulk_kernel<T, S, Q, COLL, C, NT, STAGES, XLB_TUNE_BMINB, HAS_BC>;
+    constexpr int BMINB = (XLB_TUNE_BMINB * 128 / NT) > 0 ? (XLB_TUNE_BMINB * 128 / NT) : 1;  // same register budget per thread for every NT
+    auto kern = step_bulk_kernel<T, S, Q, COLL, C, NT, STAGES, BMINB, HAS_BC>;
     static int blocks_per_sm = 0, n_sm = 0;
     const size_t smem = L::smem_bytes(STAGES);
     if (blocks_per_sm == 0) {
@@ -87,6 +88,9 @@ static int try_bulk(const StepParams& p, cudaStream_t st) {
     if (p.nz % (XLB_TUNE_NT * C) == 0) return launch_bulk<T, S, Q, COLL, C, XLB_TUNE_NT, HAS_BC>(p, st);
 #else
     if (p.nz % (128 * C) == 0) return launch_bulk<T, S, Q, COLL, C, 128, HAS_BC>(p, st);
+    if constexpr (Q == 27 && COLL == XLB_KBC) {  // narrow grids (BASELINE config 3 is 128 cells wide)
+        if (p.nz % (64 * C) == 0) return launch_bulk<T, S, Q, COLL, C, 64, HAS_BC>(p, st);
+    }
 #endif
     return -1000;
 }
