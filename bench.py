@@ -23,6 +23,7 @@ import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
+_STDOUT = sys.stdout
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
@@ -62,6 +63,18 @@ def measured_peaks():
 
 
 # --------------------------------------------------------------------------- clocks sampling
+def ncu_traffic(workload, variant):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of this workload's kernel, from the committed
+    ``ncu --set full`` capture listed in profiles/ncu_traffic.json (bytes per launch), else None."""
+    if variant != 0:
+        return None
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as fh:
+            return json.load(fh).get(workload, {}).get("dram_bytes_per_launch")
+    except (OSError, ValueError):
+        return None
+
+
 class ClockSampler:
     QUERY = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
@@ -209,6 +222,7 @@ def cpu_baseline(workload, budget_s=20.0, max_steps=8):
         "kind": "port",
         "sample": f"{steps} steps of {case['name']} ({ncell} cells), {how}; oracle port of nse_stepper.py:238-282; host has {os.cpu_count()} cores",
         "seconds": dt,
+        "steps": steps,
     }
 
 
@@ -228,7 +242,7 @@ def run_reference(args):
         "n_gpus": args.gpus,
         "steps": args.steps,
         "warmup": args.warmup,
-        "ms_per_step": None,
+        "ms_per_step": base["seconds"] / max(base["steps"], 1) * 1e3,
         "higher_is_better": True,
         "scaling": "weak",
         "vs_baseline": None,
@@ -239,7 +253,8 @@ def run_reference(args):
         "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    _STDOUT.write(json.dumps(line) + "\n")
+    _STDOUT.flush()
     return 0
 
 
@@ -338,7 +353,9 @@ def run_native(args):
             "peak": peak,
             "unit": "GB/s",
             "frac": achieved / peak,
-            "traffic": None,
+            "traffic": ncu_traffic(workload, args.variant),
+            "frac_of_nominal_8000": achieved / 8000.0,
+            "bytes_per_launch": bytes_per_launch,
             "bytes_per_cell": b_alg(vs.q, policy),
             "cells_per_launch": ncell,
             "kernel_ms": k_ms,
@@ -384,7 +401,8 @@ def run_native(args):
     if world == 1 and not args.no_cpu_baseline:
         base = cpu_baseline(workload)
         line["cpu_baseline"] = {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")}
-    print(json.dumps(line))
+    _STDOUT.write(json.dumps(line) + "\n")
+    _STDOUT.flush()
     if world > 1:
         dist.destroy_process_group()
     return 0
@@ -467,6 +485,8 @@ def main():
         # BASELINE configs[1] (512^3 D3Q19 BGK FP32FP32) per GPU; N>1 stacks N such blocks along x (weak scaling).
         # BASELINE configs[3] is `--workload cavity1024_d3q19_bgk_fp16 --strong`.
         args.workload = "cavity512_d3q19_bgk_fp32"
+    # the BC registry mirrors the reference's "registered bc ..." prints; keep stdout to the ONE JSON line
+    sys.stdout = sys.stderr
     if args.impl == "reference":
         return run_reference(args)
     return run_native(args)

@@ -23,19 +23,24 @@ def _union(faces, names, d):
     return np.unique(np.array(idx), axis=-1).tolist()
 
 
-def cavity3d(n, policy="FP32FP32", lattice="D3Q19", collision="BGK", omega=1.0, shape=None):
+def _force_tag(force):
+    return "" if force is None else "_F" + "_".join(f"{v:g}" for v in force)
+
+
+def cavity3d(n, policy="FP32FP32", lattice="D3Q19", collision="BGK", omega=1.0, shape=None, force=None):
     shape = tuple(shape) if shape else (n, n, n)
     box = bounding_box_indices(shape)
     box_ne = bounding_box_indices(shape, remove_edges=True)
     lid = box_ne["top"]
     walls = _union(box, ["bottom", "left", "right", "front", "back"], 3)
     return dict(
-        name=f"cavity3d_{'x'.join(map(str, shape))}_{lattice}_{collision}_{policy}_w{omega}",
+        name=f"cavity3d_{'x'.join(map(str, shape))}_{lattice}_{collision}_{policy}_w{omega}{_force_tag(force)}",
         lattice=lattice,
         policy=policy,
         shape=shape,
         collision=collision,
         omega=omega,
+        force=force,
         bcs=[
             dict(kind="EquilibriumBC", rho=1.0, u=(0.02, 0.0, 0.0), indices=lid),
             dict(kind="FullwayBounceBackBC", indices=walls),
@@ -43,19 +48,20 @@ def cavity3d(n, policy="FP32FP32", lattice="D3Q19", collision="BGK", omega=1.0, 
     )
 
 
-def cavity2d(n, policy="FP32FP32", collision="BGK", omega=1.6, u_lid=0.05, shape=None):
+def cavity2d(n, policy="FP32FP32", collision="BGK", omega=1.6, u_lid=0.05, shape=None, force=None):
     shape = tuple(shape) if shape else (n, n)
     box = bounding_box_indices(shape)
     box_ne = bounding_box_indices(shape, remove_edges=True)
     lid = box_ne["top"]
     walls = _union(box, ["bottom", "left", "right"], 2)
     return dict(
-        name=f"cavity2d_{'x'.join(map(str, shape))}_{collision}_{policy}_w{omega}",
+        name=f"cavity2d_{'x'.join(map(str, shape))}_{collision}_{policy}_w{omega}{_force_tag(force)}",
         lattice="D2Q9",
         policy=policy,
         shape=shape,
         collision=collision,
         omega=omega,
+        force=force,
         bcs=[
             dict(kind="HalfwayBounceBackBC", indices=walls),
             dict(kind="EquilibriumBC", rho=1.0, u=(u_lid, 0.0), indices=lid),
@@ -96,6 +102,7 @@ def sphere3d(
     profile=False,
     radius=None,
     moving_sphere=None,
+    force=None,
 ):
     shape = tuple(shape)
     box = bounding_box_indices(shape)
@@ -136,24 +143,26 @@ def sphere3d(
     if moving_sphere is not None:
         sphere_bc["prescribed_value"] = tuple(moving_sphere)
     return dict(
-        name=f"sphere3d_{'x'.join(map(str, shape))}_{lattice}_{collision}_{policy}_{inlet}_{outlet}{'_prof' if profile else ''}{'_moving' if moving_sphere is not None else ''}_w{omega}",
+        name=f"sphere3d_{'x'.join(map(str, shape))}_{lattice}_{collision}_{policy}_{inlet}_{outlet}{'_prof' if profile else ''}{'_moving' if moving_sphere is not None else ''}_w{omega}{_force_tag(force)}",
         lattice=lattice,
         policy=policy,
         shape=shape,
         collision=collision,
         omega=omega,
+        force=force,
         bcs=[dict(kind="FullwayBounceBackBC", indices=walls), inlet_bc, outlet_bc, sphere_bc],
     )
 
 
-def periodic(shape, policy="FP32FP32", lattice="D3Q19", collision="BGK", omega=1.7):
+def periodic(shape, policy="FP32FP32", lattice="D3Q19", collision="BGK", omega=1.7, force=None):
     return dict(
-        name=f"periodic_{'x'.join(map(str, shape))}_{lattice}_{collision}_{policy}_w{omega}",
+        name=f"periodic_{'x'.join(map(str, shape))}_{lattice}_{collision}_{policy}_w{omega}{_force_tag(force)}",
         lattice=lattice,
         policy=policy,
         shape=tuple(shape),
         collision=collision,
         omega=omega,
+        force=force,
         bcs=[],
     )
 
@@ -187,7 +196,7 @@ def build_oracle(case):
         else:
             raise ValueError(kind)
         bcs.append(b)
-    st = Stepper(lat, case["policy"], case["shape"], bcs, case["collision"])
+    st = Stepper(lat, case["policy"], case["shape"], bcs, case["collision"], force_vector=case.get("force"))
     return st, bcs
 
 

@@ -43,6 +43,14 @@ def golden_cases():
         (cases.sphere3d((24, 14, 14), policy="FP64FP64", inlet="pressure", outlet="extrapolation"), 10),
         (cases.sphere3d((28, 16, 16), inlet="regularized_velocity", profile=True), 30),
         (cases.sphere3d((24, 14, 14), policy="FP64FP64", inlet="regularized_pressure", lattice="D3Q19", collision="BGK"), 20),
+        # Smagorinsky LES and exact-difference forcing as extra collision cases
+        (cases.cavity3d(12, omega=1.9, collision="SmagorinskyLESBGK"), 20),
+        (cases.sphere3d((28, 16, 16), collision="SmagorinskyLESBGK", omega=1.9, inlet="regularized_velocity"), 30),
+        (cases.cavity2d(20, collision="SmagorinskyLESBGK", policy="FP64FP64", omega=1.9), 30),
+        (cases.periodic((8, 6, 8), omega=1.4, force=(1e-4, 0.0, -5e-5)), 10),
+        (cases.sphere3d((28, 16, 16), omega=1.7, force=(2e-5, 0.0, 0.0)), 30),
+        (cases.cavity3d(12, omega=1.8, collision="SmagorinskyLESBGK", policy="FP64FP64", force=(0.0, 1e-4, 0.0)), 20),
+        (cases.cavity2d(20, collision="KBC", omega=1.7, force=(1e-4, -1e-4)), 30),
     ]
 
 
@@ -90,7 +98,8 @@ def build_reference(case):
         else:
             raise ValueError(kind)
         bcs.append(b)
-    st = IncompressibleNavierStokesStepper(grid=grid, boundary_conditions=bcs, collision_type=case["collision"])
+    force = None if case.get("force") is None else jnp.array(case["force"])
+    st = IncompressibleNavierStokesStepper(grid=grid, boundary_conditions=bcs, collision_type=case["collision"], force_vector=force)
     return st
 
 

@@ -148,9 +148,49 @@ def kbc(lat, f, feq, omega, epsilon=1e-32):
     return fout
 
 
-def collide(lat, collision, f, feq, omega):
+def smagorinsky_les_bgk(lat, f, feq, omega, smagorinsky_coef=0.17):
+    """SmagorinskyLESBGK.jax_implementation, smagorinsky_les_bgk.py:44-66."""
+    dt = f.dtype.type
+    fneq = f - feq
+    pi_neq = np.tensordot(lat.cc.astype(f.dtype), fneq, axes=(0, 0))
+    if lat.d == 3:
+        diag = pi_neq[(0, 3, 5), ...]
+        offdiag = pi_neq[(1, 2, 4), ...]
+    else:
+        diag = pi_neq[(0, 2), ...]
+        offdiag = pi_neq[(1,), ...]
+    strain = np.sum(diag * diag, axis=0) + dt(2.0) * np.sum(offdiag * offdiag, axis=0)
+    tau0 = dt(1.0) / dt(omega)
+    cs = dt(smagorinsky_coef)
+    tau = dt(0.5) * (tau0 + np.sqrt(tau0 * tau0 + dt(36.0) * (cs * cs) * np.sqrt(strain)))
+    omega_eff = dt(1.0) / tau
+    fout = f - omega_eff[None, ...] * fneq
+    return fout
+
+
+def exact_difference(lat, f_postcollision, feq, rho, u, force_vector, dtype=None):
+    """ExactDifference.jax_implementation, exact_difference_force.py:52-76: f += feq(rho, u + F) - feq(rho, u)."""
+    force = np.asarray(force_vector)
+    delta_u = np.broadcast_to(force.reshape((-1,) + (1,) * (u.ndim - 1)), u.shape)
+    feq_force = quadratic_equilibrium(lat, rho, u + delta_u, dtype=dtype)
+    return f_postcollision + (feq_force - feq)
+
+
+def forced_collision(lat, collision, f, feq, omega, force_vector, dtype=None):
+    """ForcedCollision.jax_implementation, forced_collision.py:51-57: inner collision, macroscopic of the result,
+    then the forcing operator with the PRE-collision equilibrium."""
+    fout = collide(lat, collision, f, feq, omega)
+    rho, u = macroscopic(lat, fout)
+    return exact_difference(lat, fout, feq, rho, u, force_vector, dtype=dtype)
+
+
+def collide(lat, collision, f, feq, omega, force_vector=None, dtype=None):
+    if force_vector is not None:
+        return forced_collision(lat, collision, f, feq, omega, force_vector, dtype=dtype)
     if collision == "BGK":
         return bgk(f, feq, omega)
     if collision == "KBC":
         return kbc(lat, f, feq, omega)
+    if collision == "SmagorinskyLESBGK":
+        return smagorinsky_les_bgk(lat, f, feq, omega)
     raise ValueError(collision)

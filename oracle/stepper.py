@@ -13,13 +13,15 @@ from .masker import indices_boundary_masker
 
 
 class Stepper:
-    def __init__(self, lat, policy, shape, boundary_conditions=(), collision_type="BGK"):
+    def __init__(self, lat, policy, shape, boundary_conditions=(), collision_type="BGK", force_vector=None):
         self.lat = lat
         self.policy = policy
         self.cdt, self.sdt = ops.policy_dtypes(policy)
         self.shape = tuple(shape)
         self.boundary_conditions = list(boundary_conditions)
         self.collision_type = collision_type
+        # nse_stepper.py:86-87; the examples pass jnp.array(force): default float dtype == compute dtype of the policy
+        self.force_vector = None if force_vector is None else np.asarray(force_vector, dtype=self.cdt)
         if collision_type == "KBC" and not ((lat.d, lat.q) in [(2, 9), (3, 27)]):
             raise NotImplementedError("Velocity set not supported: {}".format(lat))  # kbc.py:65-66
 
@@ -51,7 +53,7 @@ class Stepper:
                 f_post_stream = bc(f_0, f_post_stream, bc_mask, missing_mask)
         rho, u = ops.macroscopic(lat, f_post_stream)  # :260
         feq = ops.quadratic_equilibrium(lat, rho, u, dtype=self.cdt)  # :263
-        f_post_collision = ops.collide(lat, self.collision_type, f_post_stream, feq, omega)  # :266
+        f_post_collision = ops.collide(lat, self.collision_type, f_post_stream, feq, omega, self.force_vector, dtype=self.cdt)  # :266
         for bc in self.boundary_conditions:  # :269-277
             f_post_collision = bc.assemble_auxiliary_data(f_post_stream, f_post_collision, bc_mask, missing_mask)
             if bc.implementation_step == COLLISION:
