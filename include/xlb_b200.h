@@ -26,12 +26,12 @@
 extern "C" {
 #endif
 
-#define XLB_B200_ABI_VERSION 1
+#define XLB_B200_ABI_VERSION 2
 
 /* element types (xlb/precision_policy.py:13-54) */
 enum { XLB_F16 = 0, XLB_F32 = 1, XLB_F64 = 2, XLB_U8 = 3 };
 /* collision models (xlb/operator/stepper/nse_stepper.py:79-87) */
-enum { XLB_BGK = 0, XLB_KBC = 1 };
+enum { XLB_BGK = 0, XLB_KBC = 1, XLB_SMAGORINSKY_LES_BGK = 2 /* smagorinsky_les_bgk.py:44-66 */ };
 /* boundary-condition kinds (xlb/operator/boundary_condition/bc_*.py) */
 enum {
     XLB_BC_NONE = 0,
@@ -72,6 +72,14 @@ typedef struct XlbDomain {
     int64_t mask_q_stride;             /* elements between directions of missing_mask */
 } XlbDomain;
 
+/* Optional parameters of the collision step beyond omega (xlb_step_ex / xlb_collide_ex). */
+typedef struct XlbCollisionParams {
+    double smagorinsky_coef; /* SmagorinskyLESBGK(smagorinsky_coef=0.17), smagorinsky_les_bgk.py:34-42 */
+    int32_t has_force;       /* != 0: ForcedCollision + ExactDifference (forced_collision.py:51-57, exact_difference_force.py:52-76) */
+    int32_t reserved;
+    double force[3];         /* force_vector in KERNEL axes (a 2-D force (Fx, Fy) is passed as (0, Fx, Fy)) */
+} XlbCollisionParams;
+
 const char* xlb_last_error(void);
 int xlb_abi_version(void);
 int xlb_bc_entry_size(void);
@@ -86,6 +94,12 @@ int xlb_step(const XlbDomain* dom, int collision, const void* f0, void* f1, cons
              const uint8_t* missing_mask, const XlbBcEntry* bc_table, int n_bc, double omega, int timestep,
              int x_begin, int x_end, int variant, void* stream);
 
+/* Same with the extra collision parameters: collision may be XLB_SMAGORINSKY_LES_BGK, and cp->has_force adds the
+ * exact-difference body force after the inner collision (nse_stepper.py:83-87).  cp == NULL behaves like xlb_step. */
+int xlb_step_ex(const XlbDomain* dom, int collision, const XlbCollisionParams* cp, const void* f0, void* f1, const uint8_t* bc_mask,
+                const uint8_t* missing_mask, const XlbBcEntry* bc_table, int n_bc, double omega, int timestep, int x_begin, int x_end,
+                int variant, void* stream);
+
 /* Stream.__call__ (stream.py:29-62): f_out[l,x] = f_in[l, x - c_l] periodic. dtype = element type. */
 int xlb_stream(const XlbDomain* dom, int dtype, const void* f_in, void* f_out, void* stream);
 /* Macroscopic / ZeroMoment / FirstMoment (macroscopic.py:21-26, zero_moment.py:14-17, first_moment.py:14-18).
@@ -97,11 +111,22 @@ int xlb_second_moment(const XlbDomain* dom, int f_dtype, const void* f, int out_
 int xlb_equilibrium(const XlbDomain* dom, int in_dtype, const void* rho, const void* u, int f_dtype, void* f, void* stream);
 /* BGK / KBC (bgk.py:27-32, kbc.py:40-79): fout = collide(f, feq, omega); all three share dtype */
 int xlb_collide(const XlbDomain* dom, int collision, int dtype, const void* f, const void* feq, void* fout, double omega, void* stream);
+/* SmagorinskyLESBGK as a stand-alone operator (smagorinsky_les_bgk.py:44-66); BGK / KBC as above; cp->has_force is not
+ * applied here (ForcedCollision composes collide + macroscopic + equilibrium on the host side, forced_collision.py:51-57) */
+int xlb_collide_ex(const XlbDomain* dom, int collision, const XlbCollisionParams* cp, int dtype, const void* f, const void* feq, void* fout,
+                   double omega, void* stream);
 /* BoundaryCondition.__call__ (boundary_condition.py:146-180 Warp kernel; bc_*.py JAX): applies BC ``id`` of
  * bc_table on cells with bc_mask == id, reading f_pre / f_post and writing f_out (may alias f_post).
  * assemble != 0 runs ExtrapolationOutflowBC.assemble_auxiliary_data (bc_extrapolation_outflow.py:106-133) instead. */
 int xlb_apply_bc(const XlbDomain* dom, int dtype, const void* f_pre, const void* f_post, void* f_out, const uint8_t* bc_mask,
                  const uint8_t* missing_mask, const XlbBcEntry* bc_table, int id, int assemble, void* stream);
+
+/* MomentumTransfer.__call__ (momentum_transfer.py:174-211, with FetchPopulations :63-70, stream-then-collide order):
+ * force[a] += sum over cells x in planes [x_begin, x_end) with bc_mask == id and a non-solid centre, and over the missing
+ * directions l, of c_opp(l)[a] * (f[opp l](x) + BC(stream(f))[l](x)).  ``force`` = 3 doubles on the device in KERNEL axes
+ * (accumulated in FP64; zero it first), f = the post-collision populations the stepper returned. */
+int xlb_momentum_transfer(const XlbDomain* dom, int dtype, const void* f_post_collision, const uint8_t* bc_mask, const uint8_t* missing_mask,
+                          const XlbBcEntry* bc_table, int id, int x_begin, int x_end, double* force, void* stream);
 
 /* IndicesBoundaryMasker (indices_boundary_masker.py:73-143), split in two device passes:
  * (1) tag: for every index column i (indices int32 [d][n], global coordinates minus ``origin``): cells outside

@@ -100,6 +100,7 @@ def build_reference(case):
         bcs.append(b)
     force = None if case.get("force") is None else jnp.array(case["force"])
     st = IncompressibleNavierStokesStepper(grid=grid, boundary_conditions=bcs, collision_type=case["collision"], force_vector=force)
+    st._golden_bcs = bcs
     return st
 
 
@@ -119,6 +120,15 @@ def run_reference(case, n_steps):
         a, b = st(a, b, bc_mask, missing, case["omega"], i)
         a, b = b, a
     out["f_n"] = np.asarray(a)
+    # MomentumTransfer on the HalfwayBounceBackBC obstacle (flow_past_sphere_3d.py:139-172) after the n steps
+    from xlb.compute_backend import ComputeBackend
+    from xlb.operator.boundary_condition import HalfwayBounceBackBC
+    from xlb.operator.force.momentum_transfer import MomentumTransfer
+
+    solids = [bc for bc in st._golden_bcs if isinstance(bc, HalfwayBounceBackBC)]
+    if solids:
+        mt = MomentumTransfer(solids[-1], compute_backend=ComputeBackend.JAX)
+        out["force_n"] = np.asarray(mt(a, b, bc_mask, missing))
     return out
 
 
@@ -141,7 +151,17 @@ def main():
         e1 = float(np.max(np.abs(one.astype(np.float64) - ref["f_one"].astype(np.float64)))) / scale
         en = float(np.max(np.abs(fn.astype(np.float64) - ref["f_n"].astype(np.float64)))) / scale
         ok_masks = bool(np.array_equal(bc_o, ref["bc_mask"]) and np.array_equal(mm_o, ref["missing_mask"]))
-        print(f"{case['name']:70s} masks_equal={ok_masks} one_step_err={e1:.2e} n_step_err={en:.2e} dtypes={ref['f_one'].dtype},{ref['f_init'].dtype}")
+        extra = {}
+        ef = ""
+        if "force_n" in ref:
+            from . import bc as obc
+            from .force import momentum_transfer
+
+            solid = [b for b in ost.boundary_conditions if isinstance(b, obc.HalfwayBounceBackBC)][-1]
+            fo = momentum_transfer(ost.lat, solid, fn, bc_o, mm_o)
+            extra["force_n"] = ref["force_n"]
+            ef = f" force={ref['force_n']} force_equal={bool(np.array_equal(fo, ref['force_n']))}"
+        print(f"{case['name']:70s} masks_equal={ok_masks} one_step_err={e1:.2e} n_step_err={en:.2e} dtypes={ref['f_one'].dtype},{ref['f_init'].dtype}{ef}")
         path = os.path.join(GOLDEN, case["name"] + ".npz")
         np.savez_compressed(
             path,
@@ -152,6 +172,7 @@ def main():
             f_one=ref["f_one"],
             f_n=ref["f_n"],
             n_steps=np.array(n_steps),
+            **extra,
         )
         index[case["name"]] = {"n_steps": n_steps, "bytes": os.path.getsize(path)}
     with open(os.path.join(GOLDEN, "INDEX.json"), "w") as fh:

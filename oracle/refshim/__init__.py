@@ -253,6 +253,8 @@ def _make_jnp():
         x = _asarray(x)
         if x.dtype == bool:
             x = x.astype(_default_int())
+        if axis is not None and not isinstance(axis, (int, tuple, list, np.integer)):
+            axis = tuple(axis)  # momentum_transfer.py:209 passes a generator expression as ``axis``
         return _wrap(np.sum(_base(x), axis=axis, keepdims=keepdims, dtype=dtype))
 
     m.sum = _sum

@@ -19,10 +19,13 @@ def load(case):
     shape = tuple(int(v) for v in z["missing_shape"])
     n = int(np.prod(shape))
     missing = np.unpackbits(z["missing_bits"])[:n].reshape(shape).astype(bool)
-    return {
+    out = {
         "bc_mask": z["bc_mask"], "missing_mask": missing, "f_init": z["f_init"], "f_one": z["f_one"], "f_n": z["f_n"],
         "n_steps": int(z["n_steps"]),
     }
+    if "force_n" in z.files:
+        out["force_n"] = z["force_n"]
+    return out
 
 
 def index():

@@ -76,6 +76,30 @@ def test_reference_analytic_identities(name, shape):
 
 @pytest.mark.parametrize("name,shape", LATS)
 @pytest.mark.parametrize("policy,dt,tol", POL)
+@pytest.mark.parametrize("omega", [0.6, 1.9])
+def test_les_and_forced_collision_operators(name, shape, policy, dt, tol, omega):
+    """SmagorinskyLESBGK (smagorinsky_les_bgk.py:44-66) and ForcedCollision + ExactDifference
+    (forced_collision.py:51-57, exact_difference_force.py:52-76) as stand-alone operators."""
+    from xlb_b200.operator.collision import BGK, ForcedCollision, SmagorinskyLESBGK
+
+    init_xlb(name, policy)
+    lat = make_lattice(name)
+    f = _rand_f(lat, shape, dt, 3)
+    rho, u = ops.macroscopic(lat, f)
+    feq = ops.quadratic_equilibrium(lat, rho, u, dtype=dt)
+    out = SmagorinskyLESBGK()(to_dev(f), to_dev(feq), omega)
+    assert rel_err(to_np(out), ops.smagorinsky_les_bgk(lat, f, feq, omega)) <= 2 * tol
+    out = SmagorinskyLESBGK(smagorinsky_coef=0.1)(to_dev(f), to_dev(feq), omega)
+    assert rel_err(to_np(out), ops.smagorinsky_les_bgk(lat, f, feq, omega, smagorinsky_coef=0.1)) <= 2 * tol
+    force = np.array([1e-3, -2e-3, 5e-4][: lat.d], dtype=dt)
+    got = ForcedCollision(collision_operator=BGK(), force_vector=force)(to_dev(f), to_dev(feq), omega)
+    ref = ops.forced_collision(lat, "BGK", f, feq, omega, force, dtype=dt)
+    assert got.dtype == to_dev(f).dtype
+    assert rel_err(to_np(got), ref) <= 4 * tol
+
+
+@pytest.mark.parametrize("name,shape", LATS)
+@pytest.mark.parametrize("policy,dt,tol", POL)
 @pytest.mark.parametrize("omega", [0.6, 1.0, 1.9])
 def test_collision(name, shape, policy, dt, tol, omega):
     from xlb_b200.operator.collision import BGK, KBC

@@ -33,3 +33,19 @@ def test_oracle_matches_reference_run(case, n_steps):
     assert rel_err(one, g["f_one"]) <= (2.0**-11 if case["policy"].endswith("FP16") else tol)
     fn, _ = ost.run(f0.astype(ost.sdt), f1, bc, mm, case["omega"], n_steps)
     assert rel_err(fn, g["f_n"]) <= (2.0**-9 if case["policy"].endswith("FP16") else 50 * tol)
+
+
+@pytest.mark.parametrize("case,n_steps", [c for c in CASES if any(b["kind"] == "HalfwayBounceBackBC" for b in c[0]["bcs"])], ids=lambda v: v["name"] if isinstance(v, dict) else str(v))
+def test_oracle_momentum_transfer_matches_reference_run(case, n_steps):
+    """oracle/force.py against MomentumTransfer of the unmodified reference (momentum_transfer.py:174-211) on the
+    reference's own populations after n steps."""
+    from oracle import bc as obc
+    from oracle.force import momentum_transfer
+
+    g = load(case)
+    ost, _ = cases.build_oracle(case)
+    solid = [b for b in ost.boundary_conditions if isinstance(b, obc.HalfwayBounceBackBC)][-1]
+    force = momentum_transfer(ost.lat, solid, g["f_n"], g["bc_mask"], g["missing_mask"])
+    assert force.shape == g["force_n"].shape == (ost.lat.d,)
+    assert force.dtype == g["force_n"].dtype
+    assert np.array_equal(force, g["force_n"])

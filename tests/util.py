@@ -68,7 +68,8 @@ def build_product(case, backend_config=None, decomposition=None):
             raise ValueError(kind)
         bcs.append(b)
     stepper = IncompressibleNavierStokesStepper(
-        grid=grid, boundary_conditions=bcs, collision_type=case["collision"], backend_config=backend_config or {}
+        grid=grid, boundary_conditions=bcs, collision_type=case["collision"], backend_config=backend_config or {},
+        force_vector=None if case.get("force") is None else np.asarray(case["force"], dtype=np.float64),
     )
     return stepper, bcs
 

@@ -16,7 +16,7 @@ from .default_config import init as init, DefaultConfig as DefaultConfig
 from . import velocity_set as velocity_set
 from . import operator as operator
 from .operator import equilibrium as _equilibrium, collision as _collision, stream as _stream  # noqa: F401
-from .operator import boundary_condition as _bc, boundary_masker as _bm, macroscopic as _macro, stepper as _stepper  # noqa: F401
+from .operator import boundary_condition as _bc, boundary_masker as _bm, macroscopic as _macro, stepper as _stepper, force as _force  # noqa: F401
 from . import grid as grid
 from . import helper as helper
 from . import distribute as distribute

@@ -10,10 +10,10 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("XLB_B200_LIB", os.path.join(_HERE, "_lib", "libxlb_b200.so"))
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 # enums of include/xlb_b200.h
-BGK, KBC = 0, 1
+BGK, KBC, SMAGORINSKY_LES_BGK = 0, 1, 2
 BC_NONE, BC_FULLWAY, BC_EQUILIBRIUM, BC_HALFWAY, BC_DONOTHING, BC_ZOUHE_VELOCITY, BC_ZOUHE_PRESSURE, BC_EXTRAPOLATION = range(8)
 BC_REGULARIZED_VELOCITY, BC_REGULARIZED_PRESSURE = 8, 9
 VARIANT_AUTO, VARIANT_SCALAR, VARIANT_VECTOR, VARIANT_GENERIC, VARIANT_BULK = range(5)
@@ -32,6 +32,15 @@ class XlbDomain(Structure):
         ("store_dtype", c_int32),
         ("q_stride", c_int64),
         ("mask_q_stride", c_int64),
+    ]
+
+
+class XlbCollisionParams(Structure):
+    _fields_ = [
+        ("smagorinsky_coef", c_double),
+        ("has_force", c_int32),
+        ("reserved", c_int32),
+        ("force", c_double * 3),
     ]
 
 
@@ -69,12 +78,15 @@ EXPORTS = {
     "xlb_domain_size": (c_int, []),
     "xlb_launch_count": (c_longlong, []),
     "xlb_step": (c_int, [POINTER(XlbDomain), c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_double, c_int, c_int, c_int, c_int, c_void_p]),
+    "xlb_step_ex": (c_int, [POINTER(XlbDomain), c_int, POINTER(XlbCollisionParams), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_double, c_int, c_int, c_int, c_int, c_void_p]),
     "xlb_stream": (c_int, [POINTER(XlbDomain), c_int, c_void_p, c_void_p, c_void_p]),
     "xlb_macroscopic": (c_int, [POINTER(XlbDomain), c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     "xlb_second_moment": (c_int, [POINTER(XlbDomain), c_int, c_void_p, c_int, c_void_p, c_void_p]),
     "xlb_equilibrium": (c_int, [POINTER(XlbDomain), c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     "xlb_collide": (c_int, [POINTER(XlbDomain), c_int, c_int, c_void_p, c_void_p, c_void_p, c_double, c_void_p]),
+    "xlb_collide_ex": (c_int, [POINTER(XlbDomain), c_int, POINTER(XlbCollisionParams), c_int, c_void_p, c_void_p, c_void_p, c_double, c_void_p]),
     "xlb_apply_bc": (c_int, [POINTER(XlbDomain), c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
+    "xlb_momentum_transfer": (c_int, [POINTER(XlbDomain), c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "xlb_mask_tag": (c_int, [POINTER(XlbDomain), c_void_p, c_int64, POINTER(c_int32), POINTER(c_int32), c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "xlb_mask_missing": (c_int, [POINTER(XlbDomain), c_void_p, POINTER(c_int32), POINTER(c_int32), c_void_p, c_void_p]),
 }

@@ -81,6 +81,12 @@ long long xlb_launch_count(void) { return g_launches.load(); }
 
 int xlb_step(const XlbDomain* dom, int collision, const void* f0, void* f1, const uint8_t* bc_mask, const uint8_t* missing_mask,
              const XlbBcEntry* bc_table, int n_bc, double omega, int timestep, int x_begin, int x_end, int variant, void* stream) {
+    return xlb_step_ex(dom, collision, nullptr, f0, f1, bc_mask, missing_mask, bc_table, n_bc, omega, timestep, x_begin, x_end, variant, stream);
+}
+
+int xlb_step_ex(const XlbDomain* dom, int collision, const XlbCollisionParams* cp, const void* f0, void* f1, const uint8_t* bc_mask,
+                const uint8_t* missing_mask, const XlbBcEntry* bc_table, int n_bc, double omega, int timestep, int x_begin, int x_end,
+                int variant, void* stream) {
     (void)timestep;  // carried for signature parity with nse_stepper.py:229; the JAX path never reads it
     if (int rc = check_domain(dom, "xlb_step")) return rc;
     if (!f0 || !f1) return set_error(XLB_EINVAL, "xlb_step: null population pointer");
@@ -108,6 +114,17 @@ int xlb_step(const XlbDomain* dom, int collision, const void* f0, void* f1, cons
     p.qs = dom->q_stride ? dom->q_stride : ncell;
     p.mqs = dom->mask_q_stride ? dom->mask_q_stride : ncell;
     p.omega = omega;
+    if (collision != XLB_BGK && collision != XLB_KBC && collision != XLB_SMAGORINSKY_LES_BGK)
+        return set_error(XLB_EINVAL, "xlb_step: unknown collision model");
+    if (collision == XLB_SMAGORINSKY_LES_BGK) {
+        const double cs = cp ? cp->smagorinsky_coef : 0.17;  // default of SmagorinskyLESBGK.__init__ (smagorinsky_les_bgk.py:39)
+        p.les_c = 36.0 * cs * cs;
+    }
+    if (cp && cp->has_force) {
+        for (int a = 0; a < 3; ++a) p.force3[a] = 3.0 * cp->force[a];
+        if (dom->d == 2) p.force3[0] = 0.0;
+        collision |= XLB_COLL_FORCED;
+    }
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int key = dom->q * 100 + dom->compute_dtype * 10 + dom->store_dtype;
     switch (key) {
@@ -186,11 +203,17 @@ int xlb_equilibrium(const XlbDomain* dom, int in_dtype, const void* rho, const v
 }
 
 int xlb_collide(const XlbDomain* dom, int collision, int dtype, const void* f, const void* feq, void* fout, double omega, void* stream) {
+    return xlb_collide_ex(dom, collision, nullptr, dtype, f, feq, fout, omega, stream);
+}
+
+int xlb_collide_ex(const XlbDomain* dom, int collision, const XlbCollisionParams* cp, int dtype, const void* f, const void* feq, void* fout,
+                   double omega, void* stream) {
     if (int rc = check_domain(dom, "xlb_collide")) return rc;
     if (!f || !feq || !fout) return set_error(XLB_EINVAL, "xlb_collide: null pointer");
     if (collision == XLB_KBC && dom->q == 19)
         return set_error(XLB_EUNSUPPORTED, "KBC: velocity set not supported (needs D2Q9 or D3Q27; kbc.py:65-66)");
-    if (collision != XLB_BGK && collision != XLB_KBC) return set_error(XLB_EINVAL, "xlb_collide: unknown collision model");
+    if (collision != XLB_BGK && collision != XLB_KBC && collision != XLB_SMAGORINSKY_LES_BGK)
+        return set_error(XLB_EINVAL, "xlb_collide: unknown collision model");
     OpParams p = make_op(dom);
     p.a = f;
     p.b = feq;
@@ -201,6 +224,9 @@ int xlb_collide(const XlbDomain* dom, int collision, int dtype, const void* f, c
     const unsigned nb = blocks_for(p.ncell, 128);
     if (collision == XLB_BGK) {
         XLB_DISPATCH_TQ(dom, (collide_kernel<T, Q, XLB_BGK><<<nb, 128, 0, st>>>(p)));
+    } else if (collision == XLB_SMAGORINSKY_LES_BGK) {
+        p.les_cs = cp ? cp->smagorinsky_coef : 0.17;
+        XLB_DISPATCH_TQ(dom, (collide_kernel<T, Q, XLB_SMAGORINSKY_LES_BGK><<<nb, 128, 0, st>>>(p)));
     } else if (dom->q == 9) {
         if (dom->compute_dtype == XLB_F64) collide_kernel<double, 9, XLB_KBC><<<nb, 128, 0, st>>>(p);
         else collide_kernel<float, 9, XLB_KBC><<<nb, 128, 0, st>>>(p);
@@ -229,6 +255,30 @@ int xlb_apply_bc(const XlbDomain* dom, int dtype, const void* f_pre, const void*
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const unsigned nb = blocks_for(p.ncell, 128);
     XLB_DISPATCH_TQ(dom, (apply_bc_kernel<T, Q><<<nb, 128, 0, st>>>(p)));
+    return count_launch(cudaGetLastError());
+}
+
+int xlb_momentum_transfer(const XlbDomain* dom, int dtype, const void* f_post_collision, const uint8_t* bc_mask, const uint8_t* missing_mask,
+                          const XlbBcEntry* bc_table, int id, int x_begin, int x_end, double* force, void* stream) {
+    if (int rc = check_domain(dom, "xlb_momentum_transfer")) return rc;
+    if (!f_post_collision || !bc_mask || !missing_mask || !bc_table || !force) return set_error(XLB_EINVAL, "xlb_momentum_transfer: null pointer");
+    if (id < 1 || id > 255) return set_error(XLB_EINVAL, "xlb_momentum_transfer: id must be in 1..255");
+    if (x_begin < 0 || x_end > dom->nx || x_begin > x_end) return set_error(XLB_EINVAL, "xlb_momentum_transfer: bad x range");
+    if (!dom->x_periodic && (x_begin < 1 || x_end > dom->nx - 1) && dom->d == 3)
+        return set_error(XLB_EINVAL, "xlb_momentum_transfer: non-periodic x needs ghost planes at x_begin-1 and x_end");
+    OpParams p = make_op(dom);
+    p.a = f_post_collision;
+    p.o0 = force;
+    p.bc_mask = bc_mask;
+    p.missing = missing_mask;
+    p.bct = bc_table;
+    p.dt_in = p.dt_out = dtype;
+    p.id = id;
+    p.flag = x_begin;
+    p.flag2 = x_end;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const unsigned nb = blocks_for(p.ncell, 128);
+    XLB_DISPATCH_TQ(dom, (momentum_transfer_kernel<T, Q><<<nb, 128, 0, st>>>(p)));
     return count_launch(cudaGetLastError());
 }
 

@@ -176,7 +176,13 @@ struct StepParams {
     long long qs;   // population stride (elements)
     long long mqs;  // missing-mask direction stride
     double omega;
+    double les_c;      // 36 * smagorinsky_coef^2 (smagorinsky_les_bgk.py:62)
+    double force3[3];  // 3 * force_vector, kernel axes (exact_difference_force.py:72-75)
 };
+
+// collision template codes: low bits = model (XLB_BGK / XLB_KBC / XLB_SMAGORINSKY_LES_BGK), bit 2 = exact-difference force
+#define XLB_COLL_FORCED 4
+#define XLB_COLL_MODEL(COLL) ((COLL) & 3)
 
 XLB_HD bool bc_is_complex(int kind) { return kind >= XLB_BC_HALFWAY; }
 

@@ -193,6 +193,9 @@ XLB_D float rcp_approx(float b) {
 XLB_D float fast_div(float a, float b) { return a * rcp_approx(b); }
 XLB_D double fast_div(double a, double b) { return a / b; }
 XLB_D F2 fast_div(F2 a, F2 b) { return a * F2{make_float2(rcp_approx(b.v.x), rcp_approx(b.v.y))}; }
+XLB_D float sqrt_of(float x) { return __fsqrt_rn(x); }
+XLB_D double sqrt_of(double x) { return sqrt(x); }
+XLB_D F2 sqrt_of(F2 x) { return {make_float2(__fsqrt_rn(x.v.x), __fsqrt_rn(x.v.y))}; }
 XLB_D float rcp_of(float x) { return __frcp_rn(x); }
 XLB_D double rcp_of(double x) { return 1.0 / x; }
 XLB_D F2 rcp_of(F2 x) { return {make_float2(__frcp_rn(x.v.x), __frcp_rn(x.v.y))}; }
@@ -272,10 +275,34 @@ XLB_D void wclass_constants(N rho, N base, N scale, N* a, N* ab) {
 // f_post[l] = f_post_stream[opp l] (bc_fullway_bounce_back.py:50-56) for lane k: the populations are swapped with
 // their opposites up front and the relaxation is switched off for that lane (omega = 0, rho = 1, 1/rho = 0 keep
 // every intermediate finite), so the fast path carries no per-direction select.
+//
+// COLL = model | XLB_COLL_FORCED: BGK (bgk.py:27-32), KBC (kbc.py:40-174), SmagorinskyLESBGK (smagorinsky_les_bgk.py:44-66:
+// BGK with a per-cell omega from the non-equilibrium stress), optionally followed by the exact-difference body force
+// (forced_collision.py:51-57, exact_difference_force.py:52-76).
+template <typename T>
+struct CollArgs {
+    T omega;
+    T les_c;      // 36 cs^2
+    T force3[3];  // 3 F, kernel axes
+};
+template <typename T>
+XLB_D CollArgs<T> coll_args(const StepParams& p) {
+    CollArgs<T> a;
+    a.omega = static_cast<T>(p.omega);
+    a.les_c = static_cast<T>(p.les_c);
+    a.force3[0] = static_cast<T>(p.force3[0]);
+    a.force3[1] = static_cast<T>(p.force3[1]);
+    a.force3[2] = static_cast<T>(p.force3[2]);
+    return a;
+}
+
 template <typename N, typename T, int Q, int COLL, int V, int J>
-XLB_D void collide_cols(T (&f)[Q][V], T omega_s, const bool* fullway, bool any_fullway) {
+XLB_D void collide_cols(T (&f)[Q][V], const CollArgs<T>& ca, const bool* fullway, bool any_fullway) {
     using S = typename Num<N>::scalar;
     constexpr int LN = Num<N>::lanes;
+    constexpr int MODEL = XLB_COLL_MODEL(COLL);
+    constexpr bool FORCED = (COLL & XLB_COLL_FORCED) != 0;
+    const T omega_s = ca.omega;
     if (any_fullway) {
 #pragma unroll
         for (int k = 0; k < LN; ++k) {
@@ -295,10 +322,10 @@ XLB_D void collide_cols(T (&f)[Q][V], T omega_s, const bool* fullway, bool any_f
     // ---- moments (zero_moment.py:14-17, first_moment.py:14-18)
     N rho = splat<N>(S(0)), sx = rho, sy = rho, sz = rho;
     bool b0 = true, bx = true, by = true, bz = true;
-    N pi[6];  // KBC: sum_l cc_l f_l, accumulated from the pair sums (cc is even in c)
+    N pi[6];  // KBC / LES: sum_l cc_l f_l, accumulated from the pair sums (cc is even in c)
 #pragma unroll
     for (int k = 0; k < 6; ++k) pi[k] = splat<N>(S(0));
-    if (COLL == XLB_KBC) {
+    if (MODEL != XLB_BGK) {
         static_for<Q>([&](auto lc) {
             XLB_IDX(l, lc);
             using D = Dir<Q, l>;
@@ -344,7 +371,28 @@ XLB_D void collide_cols(T (&f)[Q][V], T omega_s, const bool* fullway, bool any_f
     if (axis0<Q>() == 0) uu = fma_(u3[0], u3[0], uu);
     const N base = fma_(splat<N>(S(-1.0 / 6.0)), uu, splat<N>(S(1)));
     N a[4], ab[4];
-    if (COLL == XLB_BGK) {
+    if (MODEL != XLB_KBC) {
+        if (MODEL == XLB_SMAGORINSKY_LES_BGK) {
+            // Pi_neq = sum cc (f - feq) = sum cc f - rho (u u + I/3)  (exact second moment of the quadratic equilibrium);
+            // strain = sum diag^2 + 2 sum offdiag^2;  tau = (tau0 + sqrt(tau0^2 + 36 cs^2 sqrt(strain))) / 2;  omega = 1/tau
+            const N r9 = rho * splat<N>(S(1.0 / 9.0));
+            const N third = rho * splat<N>(S(1.0 / 3.0));
+            const N ry = r9 * u3[1], rz = r9 * u3[2];
+            const N pyy = fma_(-ry, u3[1], pi[3]) - third, pyz = fma_(-ry, u3[2], pi[4]), pzz = fma_(-rz, u3[2], pi[5]) - third;
+            N dsum = fma_(pzz, pzz, pyy * pyy), osum = pyz * pyz;
+            if (axis0<Q>() == 0) {
+                const N rx = r9 * u3[0];
+                const N pxx = fma_(-rx, u3[0], pi[0]) - third, pxy = fma_(-rx, u3[1], pi[1]), pxz = fma_(-rx, u3[2], pi[2]);
+                dsum = fma_(pxx, pxx, dsum);
+                osum = fma_(pxy, pxy, osum);
+                osum = fma_(pxz, pxz, osum);
+            }
+            const N strain = fma_(splat<N>(S(2)), osum, dsum);
+            const S tau0 = S(1) / static_cast<S>(omega_s);
+            const N tau = splat<N>(S(0.5)) * (splat<N>(tau0) + sqrt_of(fma_(splat<N>(static_cast<S>(ca.les_c)), sqrt_of(strain), splat<N>(tau0 * tau0))));
+            omega = rcp_of(tau);
+            if (any_fullway) omega = pick(fullway, splat<N>(S(0)), omega);
+        }
         // out = (1-omega) f + omega feq, with omega folded into the class constants
         wclass_constants<N, S, Q>(rho, base, omega, a, ab);
         const N keep = splat<N>(S(1)) - omega;
@@ -458,13 +506,69 @@ XLB_D void collide_cols(T (&f)[Q][V], T omega_s, const bool* fullway, bool any_f
             }
         });
     }
+    if constexpr (FORCED) {
+        // ForcedCollision (forced_collision.py:51-57): rho', u' = moments of the post-collision populations, then
+        // ExactDifference (exact_difference_force.py:72-75): f += feq(rho', u' + F) - feq(rho, u) with the PRE-collision
+        // equilibrium.  Full-way lanes get rho' = rho = 1, u' + F = u = 0, so their difference is exactly zero.
+        N rho2 = splat<N>(S(0)), tx = rho2, ty = rho2, tz = rho2;
+        bool c0 = true, cx = true, cy = true, cz = true;
+        static_for<Q>([&](auto lc) {
+            XLB_IDX(l, lc);
+            using D = Dir<Q, l>;
+            constexpr int o = D::o;
+            if (o == l) {
+                acc_signed<1>(rho2, c0, col_get<N>(f, l, J));
+            } else if (o > l) {
+                const N fl = col_get<N>(f, l, J), fo = col_get<N>(f, o, J);
+                const N dif = fl - fo;
+                acc_signed<1>(rho2, c0, fl + fo);
+                acc_signed<D::cx>(tx, cx, dif);
+                acc_signed<D::cy>(ty, cy, dif);
+                acc_signed<D::cz>(tz, cz, dif);
+            }
+        });
+        N inv2 = rcp_of(rho2);
+        N F3[3] = {splat<N>(static_cast<S>(ca.force3[0])), splat<N>(static_cast<S>(ca.force3[1])), splat<N>(static_cast<S>(ca.force3[2]))};
+        if (any_fullway) {
+            rho2 = pick(fullway, splat<N>(S(1)), rho2);
+            inv2 = pick(fullway, splat<N>(S(0)), inv2);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) F3[k] = pick(fullway, splat<N>(S(0)), F3[k]);
+        }
+        const N three_inv2 = splat<N>(S(3)) * inv2;
+        N v3[3];
+        v3[0] = (axis0<Q>() > 0) ? splat<N>(S(0)) : fma_(tx, three_inv2, F3[0]);
+        v3[1] = fma_(ty, three_inv2, F3[1]);
+        v3[2] = fma_(tz, three_inv2, F3[2]);
+        N vv = v3[2] * v3[2];
+        vv = fma_(v3[1], v3[1], vv);
+        if (axis0<Q>() == 0) vv = fma_(v3[0], v3[0], vv);
+        const N base2 = fma_(splat<N>(S(-1.0 / 6.0)), vv, splat<N>(S(1)));
+        N a1[4], ab1[4], a2[4], ab2[4];
+        wclass_constants<N, S, Q>(rho, base, splat<N>(S(1)), a1, ab1);
+        wclass_constants<N, S, Q>(rho2, base2, splat<N>(S(1)), a2, ab2);
+        static_for<Q>([&](auto lc) {
+            XLB_IDX(l, lc);
+            constexpr int o = Dir<Q, l>::o;
+            if (o == l) {
+                col_set<N>(f, l, J, col_get<N>(f, l, J) + (ab2[0] - ab1[0]));
+            } else if (o > l) {
+                N e1, o1, e2, o2;
+                feq_pair<N, Q, l>(u3, a1, ab1, e1, o1);
+                feq_pair<N, Q, l>(v3, a2, ab2, e2, o2);
+                const N de = e2 - e1, dd = o2 - o1;
+                col_set<N>(f, l, J, col_get<N>(f, l, J) + (de + dd));
+                col_set<N>(f, o, J, col_get<N>(f, o, J) + (de - dd));
+            }
+        });
+    }
 }
 
 // scalar entry point used by the per-cell generic engine
 template <typename T, int Q, int COLL, int V, int J>
-XLB_D void collide_column(T (&f)[Q][V], T omega, bool fullway) {
+XLB_D void collide_column(T (&f)[Q][V], const CollArgs<T>& ca, bool fullway) {
     const bool flags[1] = {fullway};
-    collide_cols<T, T, Q, COLL, V, J>(f, omega, flags, fullway);
+    collide_cols<T, T, Q, COLL, V, J>(f, ca, flags, fullway);
 }
 
 // ZouHeBC (bc_zouhe.py:165-304) on one cell: f = post-stream populations (column 0), miss = missing

@@ -18,9 +18,10 @@ struct OpParams {
     int nx, ny, nz;
     int x_periodic;
     int dt_in, dt_out;
-    int id, flag;
+    int id, flag, flag2;
     long long qs, mqs, ncell;
     double omega;
+    double les_cs;  // SmagorinskyLESBGK coefficient
 };
 
 XLB_D int wrap1o(int v, int n) { return v < 0 ? v + n : (v >= n ? v - n : v); }
@@ -121,6 +122,24 @@ __global__ void __launch_bounds__(128) collide_kernel(const __grid_constant__ Op
     if (COLL == XLB_BGK) {
 #pragma unroll
         for (int l = 0; l < Q; ++l) st_any<T>(p.o0, p.dt_out, l * p.qs + cell, f[l] - omega * (f[l] - fe[l]));
+    } else if (COLL == XLB_SMAGORINSKY_LES_BGK) {  // smagorinsky_les_bgk.py:44-66, same operation order
+        T pi[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
+        static_for<Q>([&](auto lc) {
+            XLB_IDX(l, lc);
+            acc_second_moment<Q, l>(pi, f[l] - fe[l]);
+        });
+        T dsum = pi[3] * pi[3] + pi[5] * pi[5], osum = pi[4] * pi[4];
+        if (axis0<Q>() == 0) {
+            dsum = pi[0] * pi[0] + pi[3] * pi[3] + pi[5] * pi[5];
+            osum = pi[1] * pi[1] + pi[2] * pi[2] + pi[4] * pi[4];
+        }
+        const T strain = dsum + T(2.0) * osum;
+        const T tau0 = T(1.0) / omega;
+        const T cs = static_cast<T>(p.les_cs);
+        const T tau = T(0.5) * (tau0 + sqrt(tau0 * tau0 + T(36.0) * (cs * cs) * sqrt(strain)));
+        const T omega_eff = T(1.0) / tau;
+#pragma unroll
+        for (int l = 0; l < Q; ++l) st_any<T>(p.o0, p.dt_out, l * p.qs + cell, f[l] - omega_eff * (f[l] - fe[l]));
     } else {
         T pi[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
         static_for<Q>([&](auto lc) {
@@ -145,6 +164,31 @@ __global__ void __launch_bounds__(128) collide_kernel(const __grid_constant__ Op
             const T dh = (f[l] - fe[l]) - ds;
             st_any<T>(p.o0, p.dt_out, l * p.qs + cell, f[l] - beta * (T(2.0) * ds + gamma * dh));
         });
+    }
+}
+
+// One BC kind applied to one tagged cell: f = f_post (updated in place), g = f_pre, JAX semantics of bc_*.py.
+template <typename T, int Q>
+XLB_D void bc_apply_cell(int kind, const XlbBcEntry& e, T (&f)[Q][1], const T (&g)[Q], uint32_t miss, int x, int y, int z) {
+    if (kind == XLB_BC_FULLWAY) {
+        static_for<Q>([&](auto lc) {
+            XLB_IDX(l, lc);
+            f[l][0] = g[Dir<Q, l>::o];
+        });
+    } else if (kind == XLB_BC_EQUILIBRIUM) {
+#pragma unroll
+        for (int l = 0; l < Q; ++l) f[l][0] = static_cast<T>(e.table[l]);
+    } else if (kind == XLB_BC_DONOTHING) {
+#pragma unroll
+        for (int l = 0; l < Q; ++l) f[l][0] = g[l];
+    } else if (kind == XLB_BC_HALFWAY || kind == XLB_BC_EXTRAPOLATION) {
+        static_for<Q>([&](auto lc) {
+            XLB_IDX(l, lc);
+            constexpr int o = Dir<Q, l>::o;
+            if (miss & (1u << l)) f[l][0] = (kind == XLB_BC_HALFWAY) ? g[o] + static_cast<T>(e.table[l]) : g[o];
+        });
+    } else if (kind == XLB_BC_ZOUHE_VELOCITY || kind == XLB_BC_ZOUHE_PRESSURE || kind == XLB_BC_REGULARIZED_VELOCITY || kind == XLB_BC_REGULARIZED_PRESSURE) {
+        zouhe_apply<T, Q>(f, miss, e, kind == XLB_BC_ZOUHE_VELOCITY || kind == XLB_BC_REGULARIZED_VELOCITY, x, y, z, kind >= XLB_BC_REGULARIZED_VELOCITY);
     }
 }
 
@@ -184,28 +228,63 @@ __global__ void __launch_bounds__(128) apply_bc_kernel(const __grid_constant__ O
                 }
             });
         }
-    } else if (kind == XLB_BC_FULLWAY) {
-        static_for<Q>([&](auto lc) {
-            XLB_IDX(l, lc);
-            f[l][0] = g[Dir<Q, l>::o];
-        });
-    } else if (kind == XLB_BC_EQUILIBRIUM) {
-#pragma unroll
-        for (int l = 0; l < Q; ++l) f[l][0] = static_cast<T>(e.table[l]);
-    } else if (kind == XLB_BC_DONOTHING) {
-#pragma unroll
-        for (int l = 0; l < Q; ++l) f[l][0] = g[l];
-    } else if (kind == XLB_BC_HALFWAY || kind == XLB_BC_EXTRAPOLATION) {
-        static_for<Q>([&](auto lc) {
-            XLB_IDX(l, lc);
-            constexpr int o = Dir<Q, l>::o;
-            if (miss & (1u << l)) f[l][0] = (kind == XLB_BC_HALFWAY) ? g[o] + static_cast<T>(e.table[l]) : g[o];
-        });
-    } else if (kind == XLB_BC_ZOUHE_VELOCITY || kind == XLB_BC_ZOUHE_PRESSURE || kind == XLB_BC_REGULARIZED_VELOCITY || kind == XLB_BC_REGULARIZED_PRESSURE) {
-        zouhe_apply<T, Q>(f, miss, e, kind == XLB_BC_ZOUHE_VELOCITY || kind == XLB_BC_REGULARIZED_VELOCITY, x, y, z, kind >= XLB_BC_REGULARIZED_VELOCITY);
+    } else {
+        bc_apply_cell<T, Q>(kind, e, f, g, miss, x, y, z);
     }
 #pragma unroll
     for (int l = 0; l < Q; ++l) st_any<T>(p.o0, p.dt_out, l * p.qs + cell, f[l][0]);
+}
+
+// MomentumTransfer (momentum_transfer.py:174-211) with FetchPopulations (:63-70) for the dense stream-then-collide
+// stepper: on cells tagged with the no-slip BC whose centre is not solid, f_post_stream = BC(stream(f_0)) and the
+// momentum exchanged along every missing direction l is phi_l = f_0[opp l] + f_post_stream[l], pointing along c_opp(l).
+// Per-thread sums in FP64, warp shuffle + one atomicAdd per warp into force[3] (kernel axes).  p.id = BC id,
+// [p.flag, p.flag2) = plane range that contributes (ghost planes of a slab are skipped).
+template <typename T, int Q>
+__global__ void __launch_bounds__(128) momentum_transfer_kernel(const __grid_constant__ OpParams p) {
+    const long long cell = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    double m[3] = {0.0, 0.0, 0.0};
+    if (cell < p.ncell && p.bc_mask[cell] == p.id && !p.missing[cell]) {
+        const int z = (int)(cell % p.nz);
+        const int y = (int)((cell / p.nz) % p.ny);
+        const int x = (int)(cell / ((long long)p.nz * p.ny));
+        if (x >= p.flag && x < p.flag2) {
+            const XlbBcEntry& e = p.bct[p.id];
+            T f[Q][1], g[Q];
+            uint32_t miss = 0;
+            static_for<Q>([&](auto lc) {
+                XLB_IDX(l, lc);
+                using D = Dir<Q, l>;
+                g[l] = ld_any<T>(p.a, p.dt_in, l * p.qs + cell);
+                const int xs = p.x_periodic ? wrap1o(x - D::cx, p.nx) : x - D::cx;  // ghost planes hold the neighbours
+                const int ys = wrap1o(y - D::cy, p.ny);
+                const int zs = wrap1o(z - D::cz, p.nz);
+                f[l][0] = ld_any<T>(p.a, p.dt_in, l * p.qs + ((long long)xs * p.ny + ys) * p.nz + zs);
+                miss |= (p.missing[l * p.mqs + cell] ? 1u : 0u) << l;
+            });
+            bc_apply_cell<T, Q>(e.kind, e, f, g, miss, x, y, z);
+            static_for<Q>([&](auto lc) {
+                XLB_IDX(l, lc);
+                using D = Dir<Q, l>;
+                if (miss & (1u << l)) {
+                    const double phi = static_cast<double>(g[D::o] + f[l][0]);
+                    m[0] -= D::cx * phi;  // c_opp(l) = -c_l
+                    m[1] -= D::cy * phi;
+                    m[2] -= D::cz * phi;
+                }
+            });
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+#pragma unroll
+        for (int s = 16; s > 0; s >>= 1) m[a] += __shfl_down_sync(0xffffffffu, m[a], s);
+    }
+    if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a)
+            if (m[a] != 0.0) atomicAdd(static_cast<double*>(p.o0) + a, m[a]);
+    }
 }
 
 // ------------------------------------------------------------------ indices masker (K4)

@@ -85,7 +85,7 @@ __device__ __noinline__ void cell_update_generic(const StepParams& p, int x, int
 #pragma unroll
         for (int l = 0; l < Q; ++l) fps[l] = f[l][0];
     }
-    collide_column<T, Q, COLL, 1, 0>(f, static_cast<T>(p.omega), kind == XLB_BC_FULLWAY);
+    collide_column<T, Q, COLL, 1, 0>(f, coll_args<T>(p), kind == XLB_BC_FULLWAY);
     // ---- ExtrapolationOutflowBC.assemble_auxiliary_data (bc_extrapolation_outflow.py:106-133)
     if (kind == XLB_BC_EXTRAPOLATION) {
         const T cs = T(1.0) / sqrt(T(3.0));
@@ -235,17 +235,17 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_c
             }
         }
     }
-    const T omega = static_cast<T>(p.omega);
+    const CollArgs<T> ca = coll_args<T>(p);
     // ---- collide my cells in place; FP32 runs two cells per instruction on the packed FP32 pipe (FFMA2 / FADD2 / FMUL2)
     if constexpr (XLB_PACKED(COLL) && std::is_same<T, float>::value && (V % 2 == 0)) {
         static_for<V / 2>([&](auto jc) {
             XLB_IDX(jp, jc);
-            collide_cols<F2, T, Q, COLL, V, 2 * jp>(f, omega, &k_full[2 * jp], HAS_BC && (k_full[2 * jp] || k_full[2 * jp + 1]));
+            collide_cols<F2, T, Q, COLL, V, 2 * jp>(f, ca, &k_full[2 * jp], HAS_BC && (k_full[2 * jp] || k_full[2 * jp + 1]));
         });
     } else {
         static_for<V>([&](auto jc) {
             XLB_IDX(j, jc);
-            collide_cols<T, T, Q, COLL, V, j>(f, omega, &k_full[j], HAS_BC && k_full[j]);
+            collide_cols<T, T, Q, COLL, V, j>(f, ca, &k_full[j], HAS_BC && k_full[j]);
         });
     }
     // ---- one aligned vector store per population

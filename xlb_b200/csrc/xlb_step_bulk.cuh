@@ -146,7 +146,7 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
         }
     }
 
-    const T omega = static_cast<T>(p.omega);
+    const CollArgs<T> ca = coll_args<T>(p);
     int it = 0;
     for (int t = blockIdx.x; t < total; t += gridDim.x, ++it) {
         const int s = it % STAGES;
@@ -214,12 +214,12 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
         if constexpr (XLB_PACKED(COLL) && std::is_same<T, float>::value && (C % 2 == 0)) {
             static_for<C / 2>([&](auto jc) {
                 XLB_IDX(jp, jc);
-                collide_cols<F2, T, Q, COLL, C, 2 * jp>(f, omega, &k_full[2 * jp], HAS_BC && (k_full[2 * jp] || k_full[2 * jp + 1]));
+                collide_cols<F2, T, Q, COLL, C, 2 * jp>(f, ca, &k_full[2 * jp], HAS_BC && (k_full[2 * jp] || k_full[2 * jp + 1]));
             });
         } else {
             static_for<C>([&](auto jc) {
                 XLB_IDX(j, jc);
-                collide_cols<T, T, Q, COLL, C, j>(f, omega, &k_full[j], HAS_BC && k_full[j]);
+                collide_cols<T, T, Q, COLL, C, j>(f, ca, &k_full[j], HAS_BC && k_full[j]);
             });
         }
         S* ql = f1 + (x * plane + (long long)y * p.nz + zc);

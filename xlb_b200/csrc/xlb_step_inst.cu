@@ -113,18 +113,24 @@ static int step_coll(const StepParams& p, int variant, cudaStream_t st) {
     const bool has_bc = p.bc_mask != nullptr && p.bct != nullptr;
     if (variant == XLB_VARIANT_GENERIC) return launch_generic<T, S, Q, COLL>(p, st);
     if (variant == XLB_VARIANT_BULK) {
-        const int rc = has_bc ? try_bulk<T, S, Q, COLL, true>(p, st) : try_bulk<T, S, Q, COLL, false>(p, st);
-        if (rc != -1000) return rc;
-        return set_error(XLB_EALIGN, "xlb_step: the bulk variant needs nz to be a multiple of the 256-cell tile and 16-byte aligned rows");
+        if constexpr (COLL == XLB_BGK || COLL == XLB_KBC) {
+            const int rc = has_bc ? try_bulk<T, S, Q, COLL, true>(p, st) : try_bulk<T, S, Q, COLL, false>(p, st);
+            if (rc != -1000) return rc;
+            return set_error(XLB_EALIGN, "xlb_step: the bulk variant needs nz to be a multiple of the 256-cell tile and 16-byte aligned rows");
+        } else {
+            return set_error(XLB_EUNSUPPORTED, "xlb_step: the bulk variant is built for plain BGK / KBC only");
+        }
     }
     const uintptr_t a0 = reinterpret_cast<uintptr_t>(p.f0), a1 = reinterpret_cast<uintptr_t>(p.f1);
     const bool vec_ok = (p.nz % VMAX == 0) && (p.qs % VMAX == 0) && (a0 % (VMAX * sizeof(S)) == 0) && (a1 % (VMAX * sizeof(S)) == 0) &&
                         (!has_bc || reinterpret_cast<uintptr_t>(p.bc_mask) % VMAX == 0);
     if (variant == XLB_VARIANT_VECTOR && !vec_ok) return set_error(XLB_EALIGN, "xlb_step: vector variant needs nz, q_stride and base pointers aligned to the vector width");
     // AUTO: the bulk-staged pipeline where the B200 sweeps show it ahead of the vector kernel (D3Q27 KBC, compute-heavy)
-    if (variant == XLB_VARIANT_AUTO && Q == 27 && COLL == XLB_KBC && sizeof(S) == 4) {
-        const int rc = has_bc ? try_bulk<T, S, Q, COLL, true>(p, st) : try_bulk<T, S, Q, COLL, false>(p, st);
-        if (rc != -1000) return rc;
+    if constexpr (Q == 27 && COLL == XLB_KBC && sizeof(S) == 4) {
+        if (variant == XLB_VARIANT_AUTO) {
+            const int rc = has_bc ? try_bulk<T, S, Q, COLL, true>(p, st) : try_bulk<T, S, Q, COLL, false>(p, st);
+            if (rc != -1000) return rc;
+        }
     }
     if (vec_ok && variant != XLB_VARIANT_SCALAR) {
         return has_bc ? launch_vector<T, S, Q, COLL, VMAX, true>(p, st) : launch_vector<T, S, Q, COLL, VMAX, false>(p, st);
@@ -143,10 +149,18 @@ int XLB_CAT(xlb_step_, XLB_TAG)(int collision, const xlb::StepParams& p, int var
     (void)collision; (void)p; (void)variant; (void)st;
     return set_error(XLB_EUNSUPPORTED, "xlb_step: this (lattice, policy) instance was stubbed out of a tuning build");
 #else
-    if (collision == XLB_BGK) return step_coll<XLB_TC, XLB_TS, XLB_Q, XLB_BGK>(p, variant, st);
+    // ``collision`` = model | XLB_COLL_FORCED (set by xlb_step_ex when a force vector is given)
+    switch (collision) {
+        case XLB_BGK: return step_coll<XLB_TC, XLB_TS, XLB_Q, XLB_BGK>(p, variant, st);
+        case XLB_SMAGORINSKY_LES_BGK: return step_coll<XLB_TC, XLB_TS, XLB_Q, XLB_SMAGORINSKY_LES_BGK>(p, variant, st);
+        case XLB_BGK | XLB_COLL_FORCED: return step_coll<XLB_TC, XLB_TS, XLB_Q, XLB_BGK | XLB_COLL_FORCED>(p, variant, st);
+        case XLB_SMAGORINSKY_LES_BGK | XLB_COLL_FORCED: return step_coll<XLB_TC, XLB_TS, XLB_Q, XLB_SMAGORINSKY_LES_BGK | XLB_COLL_FORCED>(p, variant, st);
 #if XLB_Q != 19
-    if (collision == XLB_KBC) return step_coll<XLB_TC, XLB_TS, XLB_Q, XLB_KBC>(p, variant, st);
+        case XLB_KBC: return step_coll<XLB_TC, XLB_TS, XLB_Q, XLB_KBC>(p, variant, st);
+        case XLB_KBC | XLB_COLL_FORCED: return step_coll<XLB_TC, XLB_TS, XLB_Q, XLB_KBC | XLB_COLL_FORCED>(p, variant, st);
 #endif
+        default: break;
+    }
     return set_error(XLB_EUNSUPPORTED, "xlb_step: collision model not supported for this velocity set (KBC needs D2Q9 or D3Q27; kbc.py:65-66)");
 #endif
 }

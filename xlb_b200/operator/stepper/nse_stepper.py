@@ -17,7 +17,7 @@ from ...helper.check_boundary_overlaps import check_bc_overlaps
 from ...helper.nse_fields import create_nse_fields
 from ..boundary_condition.boundary_condition import ImplementationStep
 from ..boundary_masker import IndicesBoundaryMasker
-from ..collision import BGK, KBC
+from ..collision import BGK, KBC, ForcedCollision, SmagorinskyLESBGK
 from ..equilibrium import QuadraticEquilibrium
 from ..macroscopic import Macroscopic
 from ..operator import Operator, byref, check, lib, stream_ptr
@@ -42,10 +42,15 @@ class IncompressibleNavierStokesStepper(Stepper):
             self.collision = BGK(self.velocity_set, self.precision_policy, self.compute_backend)
         elif collision_type == "KBC":
             self.collision = KBC(self.velocity_set, self.precision_policy, self.compute_backend)
+        elif collision_type == "SmagorinskyLESBGK":
+            self.collision = SmagorinskyLESBGK(self.velocity_set, self.precision_policy, self.compute_backend)
         else:
-            raise NotImplementedError(f"collision_type={collision_type!r} is outside the scope of the CUDA backend (BGK and KBC are implemented)")
-        if force_vector is not None:
-            raise NotImplementedError("forcing (ForcedCollision / ExactDifference) is outside the scope of the CUDA backend")
+            raise NotImplementedError(f"collision_type={collision_type!r}: expected 'BGK', 'KBC' or 'SmagorinskyLESBGK' (nse_stepper.py:79-84)")
+        if force_vector is not None:  # nse_stepper.py:86-87
+            if not hasattr(force_vector, "shape"):
+                force_vector = np.asarray(force_vector, dtype=np.float64)
+            self.collision = ForcedCollision(collision_operator=self.collision, forcing_scheme=forcing_scheme, force_vector=force_vector)
+        self._collision_params = self.collision.abi_params()
         self.streaming_scheme = streaming_scheme
         if streaming_scheme != "pull":
             raise NotImplementedError(f"Unknown or unimplemented streaming scheme for backend: {self.compute_backend}")  # nse_stepper.py:91-92
@@ -129,8 +134,9 @@ class IncompressibleNavierStokesStepper(Stepper):
         if n_bc:
             self._check_field(bc_mask, "bc_mask", 1)
             self._check_field(missing_mask, "missing_mask", q)
-        rc = lib().xlb_step(
-            byref(dom), self.collision.abi_model, f_0.data_ptr(), f_1.data_ptr(),
+        cp = self._collision_params
+        rc = lib().xlb_step_ex(
+            byref(dom), self.collision.abi_model, byref(cp) if cp is not None else None, f_0.data_ptr(), f_1.data_ptr(),
             bc_mask.data_ptr() if n_bc else None, missing_mask.data_ptr() if n_bc else None, table.data_ptr() if n_bc else None, n_bc,
             float(omega), int(timestep), int(x_begin), int(x_end), self.kernel_variant, stream_ptr(),
         )
