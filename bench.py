@@ -40,9 +40,13 @@ WORKLOADS = {
     "sphere768_d3q27_kbc_fp32": ("D3Q27", "KBC", "FP32FP32", (768, 256, 256), 1.6, "sphere"),
     "sphere384x256x512_d3q27_kbc_fp32": ("D3Q27", "KBC", "FP32FP32", (384, 256, 512), 1.6, "sphere"),
     "cavity384x256x512_d3q27_bgk_fp32": ("D3Q27", "BGK", "FP32FP32", (384, 256, 512), 1.7, "cavity"),
+    "cavity768x256x256_d3q27_kbc_fp32": ("D3Q27", "KBC", "FP32FP32", (768, 256, 256), 1.6, "cavity"),
     "cavity768_d3q19_bgk_fp16": ("D3Q19", "BGK", "FP32FP16", (512, 768, 768), 1.0, "cavity"),
     "cavity1024_d3q19_bgk_fp16": ("D3Q19", "BGK", "FP32FP16", (1024, 1024, 1024), 1.0, "cavity"),
     "cavity640_d3q19_bgk_fp16": ("D3Q19", "BGK", "FP32FP16", (640, 640, 640), 1.0, "cavity"),
+    # BASELINE configs[4] (windtunnel_3d.py with a sphere instead of the STL car): 1536 x 1536 cross-section,
+    # 192 planes per GPU (weak scaling: 1536^3 on 8 GPUs); omega from Re = 50 000 like windtunnel_3d.py:42-45
+    "windtunnel192x1536x1536_d3q27_kbc_fp32": ("D3Q27", "KBC", "FP32FP32", (192, 1536, 1536), 1.0 / (3.0 * (0.02 * 1535 / 50000.0) + 0.5), "windtunnel"),
 }
 STORE_BYTES = {"FP32FP32": 4, "FP64FP64": 8, "FP32FP16": 2, "FP64FP32": 4, "FP64FP16": 2}
 DTYPE_NAME = {"FP32FP32": "f32", "FP64FP64": "f64", "FP32FP16": "f32 (f16 storage)", "FP64FP32": "f64 (f32 storage)", "FP64FP16": "f64 (f16 storage)"}
@@ -164,13 +168,20 @@ def build_case(workload, slab=None, shape=None, variant=0):
     else:  # examples/cfd/flow_past_sphere_3d.py:38-113 with Zou-He inlet (BASELINE config 3)
         r = ny // 12
         cx, cy, cz = nx // 6, ny // 2, nz // 2
+        u_in = 0.04
+        if kind == "windtunnel":  # windtunnel_3d.py:78-106 with a sphere obstacle
+            r = min(ny // 8, nx // 4)
+            cx = nx // 3
+            u_in = 0.02
         xs = np.arange(max(cx - r, 0), min(cx + r + 1, nx))
-        X, Y, Z = np.meshgrid(xs, np.arange(ny), np.arange(nz), indexing="ij")
+        ys = np.arange(max(cy - r, 0), min(cy + r + 1, ny))
+        zs = np.arange(max(cz - r, 0), min(cz + r + 1, nz))
+        X, Y, Z = np.meshgrid(xs, ys, zs, indexing="ij")
         sel = (X - cx) ** 2 + (Y - cy) ** 2 + (Z - cz) ** 2 < r**2
         sphere = np.stack([X[sel], Y[sel], Z[sel]])
         bcs = [
             FullwayBounceBackBC(indices=union(["bottom", "top", "front", "back"])),
-            ZouHeBC("velocity", prescribed_value=(0.04, 0.0, 0.0), indices=box_ne["left"]),
+            ZouHeBC("velocity", prescribed_value=(u_in, 0.0, 0.0), indices=box_ne["left"]),
             ExtrapolationOutflowBC(indices=box_ne["right"]),
             HalfwayBounceBackBC(indices=sphere),
         ]
@@ -281,6 +292,8 @@ def run_native(args):
 
     workload = args.workload
     lattice, collision, policy, shape, omega, kind = WORKLOADS[workload]
+    if args.shape:
+        shape = tuple(int(v) for v in args.shape.split(","))
     if world > 1 and not args.strong:
         shape = (shape[0] * world,) + tuple(shape[1:])  # weak scaling: the N=1 block per GPU, stacked along x
     stepper, vs, pol, shape, omega = build_case(workload, slab=slab, shape=shape, variant=args.variant)
@@ -479,6 +492,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-overlap", action="store_true")
     ap.add_argument("--variant", type=int, default=0, help="kernel variant of xlb_step (0 auto, 2 vector, 3 generic, 4 bulk-staged)")
+    ap.add_argument("--shape", default=None, help="override the workload's shape, e.g. 48,1536,1536 (experiments only; config.shape reports it)")
     ap.add_argument("--strong", action="store_true", help="N>1: keep the global shape of the workload (strong scaling) instead of one block per GPU")
     args = ap.parse_args()
     if args.workload is None:

@@ -29,6 +29,7 @@ def main():
         (cases.sphere3d((12 * world if world > 2 else 36, 24, 24)), 25),
         (cases.cavity3d(0, shape=(6 * world + 1, 10, 8), lattice="D3Q27", collision="KBC", omega=1.8, policy="FP64FP64"), 10),  # uneven slabs
         (cases.cavity3d(0, shape=(4 * world, 16, 16), policy="FP32FP16", omega=1.5), 10),
+        (cases.sphere3d((12 * world if world > 2 else 36, 24, 24), collision="SmagorinskyLESBGK", omega=1.9, force=(2e-5, 0.0, 1e-5)), 10),
     ]
     for case, nsteps in todo:
         for overlap in (True, False):
@@ -61,6 +62,18 @@ def main():
             if not (same and same_all):
                 d = (dst.owned(g_0).double() - ref[:, x0 : x0 + n].double()).abs().max().item()
                 raise AssertionError(f"rank {rank}: {case['name']} overlap={overlap}: distributed != single GPU (max abs diff {d:.3e})")
+            # MomentumTransfer on the obstacle: slab partial sums all-reduced == single-GPU value (to FP64 summation order)
+            from xlb_b200.operator.boundary_condition import HalfwayBounceBackBC
+            from xlb_b200.operator.force import MomentumTransfer
+
+            solids = [b for b in st.boundary_conditions if isinstance(b, HalfwayBounceBackBC)]
+            if solids and overlap:
+                st1, _ = build_product(case)
+                solid1 = [b for b in st1.boundary_conditions if isinstance(b, HalfwayBounceBackBC)][-1]
+                f_ref = MomentumTransfer(solid1)(ref, f_1, ref_bc, ref_mm)
+                f_dist = MomentumTransfer(solids[-1], grid=st.grid)(g_0, g_1, g_bc, g_mm)
+                err = (f_ref.double() - f_dist.double()).abs().max().item() / f_ref.double().abs().max().item()
+                assert err < 1e-6, f"rank {rank}: MomentumTransfer distributed {f_dist.tolist()} != single {f_ref.tolist()}"
             if rank == 0:
                 print(f"OK {case['name']} world={world} overlap={overlap} steps={nsteps}: bitwise equal to the single-GPU run", flush=True)
     dist.barrier()
