@@ -130,7 +130,7 @@ class ClockSampler:
 
 
 # --------------------------------------------------------------------------- case construction (product objects)
-def build_case(workload, slab=None, shape=None, variant=0):
+def build_case(workload, slab=None, shape=None, variant=0, radius=None):
     """Product-side objects of a workload.  BC index sets are generated per slab (global coords) so that the
     1536^3-class cases never materialise a global index list on one rank."""
     import numpy as np
@@ -173,6 +173,8 @@ def build_case(workload, slab=None, shape=None, variant=0):
             r = min(ny // 8, nx // 4)
             cx = nx // 3
             u_in = 0.02
+        if radius is not None:
+            r = int(radius)
         xs = np.arange(max(cx - r, 0), min(cx + r + 1, nx))
         ys = np.arange(max(cy - r, 0), min(cy + r + 1, ny))
         zs = np.arange(max(cz - r, 0), min(cz + r + 1, nz))
@@ -296,7 +298,7 @@ def run_native(args):
         shape = tuple(int(v) for v in args.shape.split(","))
     if world > 1 and not args.strong:
         shape = (shape[0] * world,) + tuple(shape[1:])  # weak scaling: the N=1 block per GPU, stacked along x
-    stepper, vs, pol, shape, omega = build_case(workload, slab=slab, shape=shape, variant=args.variant)
+    stepper, vs, pol, shape, omega = build_case(workload, slab=slab, shape=shape, variant=args.variant, radius=args.radius)
     if slab is not None:
         from xlb_b200.distribute import distribute
 
@@ -373,6 +375,18 @@ def run_native(args):
             "cells_per_launch": ncell,
             "kernel_ms": k_ms,
             "peak_source": peak_src,
+        }
+
+    if world > 1:
+        # per-GPU roofline of the whole distributed step (two edge-plane launches + interior launch + halo ring):
+        # algorithmic bytes of one rank's slab over the max-over-ranks step time
+        per_rank = b_alg(vs.q, policy) * (ncell // world)
+        achieved = per_rank / (ms / args.steps * 1e-3) / 1e9
+        roofline = {
+            "bound": "hbm", "kernel": "per-GPU slab step (2 edge-plane launches + interior launch, halo exchange overlapped)",
+            "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+            "frac_of_nominal_8000": achieved / 8000.0, "bytes_per_launch": per_rank, "bytes_per_cell": b_alg(vs.q, policy),
+            "cells_per_launch": ncell // world, "kernel_ms": ms / args.steps, "peak_source": peak_src,
         }
 
     # ---- e2e: HOST buffers in, HOST buffers out (pinned), copies inside the timed region
@@ -492,6 +506,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-overlap", action="store_true")
     ap.add_argument("--variant", type=int, default=0, help="kernel variant of xlb_step (0 auto, 2 vector, 3 generic, 4 bulk-staged)")
+    ap.add_argument("--radius", type=int, default=None, help="override the obstacle radius of the sphere / wind-tunnel workloads (experiments only)")
     ap.add_argument("--shape", default=None, help="override the workload's shape, e.g. 48,1536,1536 (experiments only; config.shape reports it)")
     ap.add_argument("--strong", action="store_true", help="N>1: keep the global shape of the workload (strong scaling) instead of one block per GPU")
     args = ap.parse_args()

@@ -76,8 +76,11 @@ typedef struct XlbDomain {
 typedef struct XlbCollisionParams {
     double smagorinsky_coef; /* SmagorinskyLESBGK(smagorinsky_coef=0.17), smagorinsky_les_bgk.py:34-42 */
     int32_t has_force;       /* != 0: ForcedCollision + ExactDifference (forced_collision.py:51-57, exact_difference_force.py:52-76) */
-    int32_t reserved;
+    int32_t bc_kind_mask;    /* OR of (1 << XLB_BC_*) over the kinds in bc_table; 0 = unknown.  Lets the library pick the leanest
+                                kernel instance (e.g. without the vectorised half-way bounce-back path) */
     double force[3];         /* force_vector in KERNEL axes (a 2-D force (Fx, Fy) is passed as (0, Fx, Fy)) */
+    double halfway_fraction; /* hint: fraction of the block's cells tagged with a HalfwayBounceBackBC (obstacle interiors
+                                included); 0 = unknown / none.  Only steers the choice between kernel variants */
 } XlbCollisionParams;
 
 const char* xlb_last_error(void);

@@ -39,8 +39,9 @@ class XlbCollisionParams(Structure):
     _fields_ = [
         ("smagorinsky_coef", c_double),
         ("has_force", c_int32),
-        ("reserved", c_int32),
+        ("bc_kind_mask", c_int32),
         ("force", c_double * 3),
+        ("halfway_fraction", c_double),
     ]
 
 

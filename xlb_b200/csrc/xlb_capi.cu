@@ -114,6 +114,8 @@ int xlb_step_ex(const XlbDomain* dom, int collision, const XlbCollisionParams* c
     p.qs = dom->q_stride ? dom->q_stride : ncell;
     p.mqs = dom->mask_q_stride ? dom->mask_q_stride : ncell;
     p.omega = omega;
+    p.bc_kind_mask = cp ? cp->bc_kind_mask : 0;
+    p.halfway_fraction = cp ? (float)cp->halfway_fraction : 0.f;
     if (collision != XLB_BGK && collision != XLB_KBC && collision != XLB_SMAGORINSKY_LES_BGK)
         return set_error(XLB_EINVAL, "xlb_step: unknown collision model");
     if (collision == XLB_SMAGORINSKY_LES_BGK) {

@@ -176,6 +176,8 @@ struct StepParams {
     long long qs;   // population stride (elements)
     long long mqs;  // missing-mask direction stride
     double omega;
+    float halfway_fraction;  // hint for the variant choice (see XlbCollisionParams)
+    int bc_kind_mask;  // bit k set: a BC of kind k may be present (0 = unknown, assume any)
     double les_c;      // 36 * smagorinsky_coef^2 (smagorinsky_les_bgk.py:62)
     double force3[3];  // 3 * force_vector, kernel axes (exact_difference_force.py:72-75)
 };

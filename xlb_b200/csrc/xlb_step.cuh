@@ -133,7 +133,10 @@ XLB_D __half ld_if(const __half* ptr, bool pred, __half keep) {
     return __ushort_as_half(k);
 }
 
-template <typename T, typename S, int Q, int COLL, int V, int BLOCK, int MINB, bool HAS_BC>
+// HALF: the BC list holds a HalfwayBounceBackBC; its cells (obstacle surface AND interior -- every solid cell is tagged)
+// then take a vectorised in-register path instead of the per-cell generic engine.  It is a template flag because the
+// fast path of this kernel is register-critical: compiling the extra path into the BC-free / cavity instance costs 5-8 %.
+template <typename T, typename S, int Q, int COLL, int V, int BLOCK, int MINB, bool HAS_BC, bool HALF = false>
 __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_constant__ StepParams p) {
     const S* __restrict__ f0 = static_cast<const S*>(p.f0);
     S* __restrict__ f1 = static_cast<S*>(p.f1);
@@ -157,10 +160,10 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_c
 
     // ---- packed bc ids of my V cells
     uint8_t ids[V];
-    bool any_bc = false, slow = false;
-    bool k_full[V], k_eq[V];
+    bool any_bc = false, slow = false, any_half = false;
+    bool k_full[V], k_eq[V], k_half[V];
 #pragma unroll
-    for (int j = 0; j < V; ++j) k_full[j] = k_eq[j] = false;
+    for (int j = 0; j < V; ++j) k_full[j] = k_eq[j] = k_half[j] = false;
     if (HAS_BC) {
         const Vec<uint8_t, V> w = ld_vec<uint8_t, V>(p.bc_mask + cell);
 #pragma unroll
@@ -175,7 +178,13 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_c
                     const int k = p.bct[ids[j]].kind;
                     k_full[j] = k == XLB_BC_FULLWAY;
                     k_eq[j] = k == XLB_BC_EQUILIBRIUM;
-                    slow |= bc_is_complex(k);
+                    if constexpr (HALF) {
+                        k_half[j] = k == XLB_BC_HALFWAY;
+                        any_half |= k_half[j];
+                        slow |= bc_is_complex(k) && !k_half[j];
+                    } else {
+                        slow |= bc_is_complex(k);
+                    }
                 }
             }
         }
@@ -223,6 +232,32 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_c
         // a BC kind that needs f_pre / missing_mask / neighbour gathers: per-cell generic engine
         for (int j = 0; j < V; ++j) cell_update_generic<T, S, Q, COLL>(p, x, y, z0 + j);
         return;
+    }
+    if constexpr (HAS_BC && HALF) {
+        if (any_half) {
+            // HalfwayBounceBackBC, STREAMING step (bc_halfway_bounce_back.py:116-134): where missing[l],
+            // f_post[l] = f_pre[opp l] (+ 6 w_l c_l.u_wall) of the same cell.  Two phases of independent vector loads
+            // (all mask bytes, then all opposite populations) so no load waits on another.
+            uint32_t mb[V];
+#pragma unroll
+            for (int j = 0; j < V; ++j) mb[j] = 0;
+            static_for<Q>([&](auto lc) {
+                XLB_IDX(l, lc);
+                const Vec<uint8_t, V> m = ld_vec<uint8_t, V>(p.missing + l * p.mqs + cell);
+#pragma unroll
+                for (int j = 0; j < V; ++j) mb[j] |= (m.v[j] ? 1u : 0u) << l;
+            });
+#pragma unroll
+            for (int j = 0; j < V; ++j)
+                if (!k_half[j]) mb[j] = 0;
+            static_for<Q>([&](auto lc) {
+                XLB_IDX(l, lc);
+                const Vec<S, V> g = ld_vec<S, V>(f0 + Dir<Q, l>::o * p.qs + cell);
+#pragma unroll
+                for (int j = 0; j < V; ++j)
+                    if (mb[j] & (1u << l)) f[l][j] = to_compute<T, S>(g.v[j]) + static_cast<T>(p.bct[ids[j]].table[l]);
+            });
+        }
     }
     if (HAS_BC && any_bc) {
         // EquilibriumBC (STREAMING step): f_post_stream = feq(rho_bc, u_bc) constants

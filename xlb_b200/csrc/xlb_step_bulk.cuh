@@ -67,7 +67,7 @@ struct BulkLayout {
     static size_t smem_bytes(int stages) { return (size_t)stages * STAGE_BYTES + 128; }
 };
 
-template <typename T, typename S, int Q, int COLL, int C, int NT, int STAGES, int MINB, bool HAS_BC>
+template <typename T, typename S, int Q, int COLL, int C, int NT, int STAGES, int MINB, bool HAS_BC, bool HALF = false>
 __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_constant__ StepParams p) {
     constexpr int TZ = NT * C;
     using L = BulkLayout<S, Q, TZ, HAS_BC>;
@@ -181,10 +181,10 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
         prev = __shfl_sync(0xffffffffu, prev, 0);
         if ((prev + 1) % NW == 0 && (long long)t + (long long)STAGES * gridDim.x < total) issue(t + STAGES * (int)gridDim.x, s);
 
-        bool slow = false;
-        bool k_full[C], k_eq[C];
+        bool slow = false, any_half = false;
+        bool k_full[C], k_eq[C], k_half[C];
 #pragma unroll
-        for (int j = 0; j < C; ++j) k_full[j] = k_eq[j] = false;
+        for (int j = 0; j < C; ++j) k_full[j] = k_eq[j] = k_half[j] = false;
         if (HAS_BC && any_bc) {
 #pragma unroll
             for (int j = 0; j < C; ++j) {
@@ -192,7 +192,13 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
                     const int k = p.bct[ids[j]].kind;
                     k_full[j] = k == XLB_BC_FULLWAY;
                     k_eq[j] = k == XLB_BC_EQUILIBRIUM;
-                    slow |= bc_is_complex(k);
+                    if constexpr (HALF) {  // see step_vector_kernel
+                        k_half[j] = k == XLB_BC_HALFWAY;
+                        any_half |= k_half[j];
+                        slow |= bc_is_complex(k) && !k_half[j];
+                    } else {
+                        slow |= bc_is_complex(k);
+                    }
                 }
             }
         }
@@ -200,6 +206,32 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
         if (HAS_BC && slow) {
             for (int j = 0; j < C; ++j) cell_update_generic<T, S, Q, COLL>(p, x, y, zc + j * NT);
             continue;
+        }
+        if constexpr (HAS_BC && HALF) {
+            if (any_half) {
+                // HalfwayBounceBackBC, STREAMING step (bc_halfway_bounce_back.py:116-134), coalesced and in two phases of
+                // independent loads: all mask bytes, then all opposite populations of the same cell
+                const long long cell0 = x * plane + (long long)y * p.nz + zc;
+                uint32_t mb[C];
+#pragma unroll
+                for (int j = 0; j < C; ++j) mb[j] = 0;
+                static_for<Q>([&](auto lc) {
+                    XLB_IDX(l, lc);
+#pragma unroll
+                    for (int j = 0; j < C; ++j) mb[j] |= (p.missing[l * p.mqs + cell0 + j * NT] ? 1u : 0u) << l;
+                });
+#pragma unroll
+                for (int j = 0; j < C; ++j)
+                    if (!k_half[j]) mb[j] = 0;
+                static_for<Q>([&](auto lc) {
+                    XLB_IDX(l, lc);
+#pragma unroll
+                    for (int j = 0; j < C; ++j) {
+                        const T g = to_compute<T, S>(f0[Dir<Q, l>::o * p.qs + cell0 + j * NT]);
+                        if (mb[j] & (1u << l)) f[l][j] = g + static_cast<T>(p.bct[ids[j]].table[l]);
+                    }
+                });
+            }
         }
         if (HAS_BC && any_bc) {
 #pragma unroll

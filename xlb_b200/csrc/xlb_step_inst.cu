@@ -21,7 +21,7 @@ constexpr int default_minb() { return sizeof(S) == 8 ? 4 : (Q == 27 ? 4 : (sizeo
 
 namespace xlb {
 
-template <typename T, typename S, int Q, int COLL, int V, bool HAS_BC>
+template <typename T, typename S, int Q, int COLL, int V, bool HAS_BC, bool HALF = false>
 static int launch_vector(const StepParams& p0, cudaStream_t st) {
     constexpr int BLOCK = XLB_TUNE_BLOCK;
     StepParams p = p0;
@@ -36,7 +36,7 @@ static int launch_vector(const StepParams& p0, cudaStream_t st) {
 #else
     constexpr int MINB = (V == 1) ? 4 : default_minb<S, Q>();
 #endif
-    step_vector_kernel<T, S, Q, COLL, V, BLOCK, MINB, HAS_BC><<<grid, BLOCK, 0, st>>>(p);
+    step_vector_kernel<T, S, Q, COLL, V, BLOCK, MINB, HAS_BC, HALF><<<grid, BLOCK, 0, st>>>(p);
     return count_launch(cudaGetLastError());
 }
 
@@ -51,13 +51,13 @@ static int launch_vector(const StepParams& p0, cudaStream_t st) {
 #endif
 
 // persistent bulk-copy-staged kernel (xlb_step_bulk.cuh); returns -1000 when the shape does not qualify
-template <typename T, typename S, int Q, int COLL, int C, int NT, bool HAS_BC>
+template <typename T, typename S, int Q, int COLL, int C, int NT, bool HAS_BC, bool HALF = false>
 static int launch_bulk(const StepParams& p, cudaStream_t st) {
     constexpr int TZ = NT * C;
     constexpr int STAGES = XLB_TUNE_STAGES;
     using L = BulkLayout<S, Q, TZ, HAS_BC>;
     constexpr int BMINB = (XLB_TUNE_BMINB * 128 / NT) > 0 ? (XLB_TUNE_BMINB * 128 / NT) : 1;  // same register budget per thread for every NT
-    auto kern = step_bulk_kernel<T, S, Q, COLL, C, NT, STAGES, BMINB, HAS_BC>;
+    auto kern = step_bulk_kernel<T, S, Q, COLL, C, NT, STAGES, BMINB, HAS_BC, HALF>;
     static int blocks_per_sm = 0, n_sm = 0;
     const size_t smem = L::smem_bytes(STAGES);
     if (blocks_per_sm == 0) {
@@ -78,18 +78,18 @@ static int launch_bulk(const StepParams& p, cudaStream_t st) {
     return count_launch(cudaGetLastError());
 }
 
-template <typename T, typename S, int Q, int COLL, bool HAS_BC>
+template <typename T, typename S, int Q, int COLL, bool HAS_BC, bool HALF = false>
 static int try_bulk(const StepParams& p, cudaStream_t st) {
     constexpr int C = XLB_TUNE_C;
     const uintptr_t a0 = reinterpret_cast<uintptr_t>(p.f0), am = reinterpret_cast<uintptr_t>(p.bc_mask);
     const bool aligned = (a0 % 16 == 0) && ((p.qs * sizeof(S)) % 16 == 0) && ((p.nz * sizeof(S)) % 16 == 0) && (!HAS_BC || am % 16 == 0);
     if (!aligned) return -1000;
 #ifdef XLB_TUNE_NT
-    if (p.nz % (XLB_TUNE_NT * C) == 0) return launch_bulk<T, S, Q, COLL, C, XLB_TUNE_NT, HAS_BC>(p, st);
+    if (p.nz % (XLB_TUNE_NT * C) == 0) return launch_bulk<T, S, Q, COLL, C, XLB_TUNE_NT, HAS_BC, HALF>(p, st);
 #else
-    if (p.nz % (128 * C) == 0) return launch_bulk<T, S, Q, COLL, C, 128, HAS_BC>(p, st);
+    if (p.nz % (128 * C) == 0) return launch_bulk<T, S, Q, COLL, C, 128, HAS_BC, HALF>(p, st);
     if constexpr (Q == 27 && COLL == XLB_KBC) {  // narrow grids (BASELINE config 3 is 128 cells wide)
-        if (p.nz % (64 * C) == 0) return launch_bulk<T, S, Q, COLL, C, 64, HAS_BC>(p, st);
+        if (p.nz % (64 * C) == 0) return launch_bulk<T, S, Q, COLL, C, 64, HAS_BC, HALF>(p, st);
     }
 #endif
     return -1000;
@@ -111,10 +111,20 @@ static int step_coll(const StepParams& p, int variant, cudaStream_t st) {
     constexpr int VMAX = default_vec<S, Q>();
 #endif
     const bool has_bc = p.bc_mask != nullptr && p.bct != nullptr;
+    // half-way obstacles get the instance with the vectorised half-way path (unknown kind mask: assume present)
+    const bool half = has_bc && (p.bc_kind_mask == 0 || (p.bc_kind_mask & (1 << XLB_BC_HALFWAY)));
+    auto bulk = [&]() -> int {
+        if constexpr (COLL == XLB_BGK || COLL == XLB_KBC) {
+            if (!has_bc) return try_bulk<T, S, Q, COLL, false>(p, st);
+            return half ? try_bulk<T, S, Q, COLL, true, true>(p, st) : try_bulk<T, S, Q, COLL, true, false>(p, st);
+        } else {
+            return -1000;
+        }
+    };
     if (variant == XLB_VARIANT_GENERIC) return launch_generic<T, S, Q, COLL>(p, st);
     if (variant == XLB_VARIANT_BULK) {
         if constexpr (COLL == XLB_BGK || COLL == XLB_KBC) {
-            const int rc = has_bc ? try_bulk<T, S, Q, COLL, true>(p, st) : try_bulk<T, S, Q, COLL, false>(p, st);
+            const int rc = bulk();
             if (rc != -1000) return rc;
             return set_error(XLB_EALIGN, "xlb_step: the bulk variant needs nz to be a multiple of the 256-cell tile and 16-byte aligned rows");
         } else {
@@ -127,13 +137,16 @@ static int step_coll(const StepParams& p, int variant, cudaStream_t st) {
     if (variant == XLB_VARIANT_VECTOR && !vec_ok) return set_error(XLB_EALIGN, "xlb_step: vector variant needs nz, q_stride and base pointers aligned to the vector width");
     // AUTO: the bulk-staged pipeline where the B200 sweeps show it ahead of the vector kernel (D3Q27 KBC, compute-heavy)
     if constexpr (Q == 27 && COLL == XLB_KBC && sizeof(S) == 4) {
-        if (variant == XLB_VARIANT_AUTO) {
-            const int rc = has_bc ? try_bulk<T, S, Q, COLL, true>(p, st) : try_bulk<T, S, Q, COLL, false>(p, st);
+        // ... except on blocks where a large half-way obstacle covers more than ~1 % of the cells: the direct loads of its
+        // bounce-back path are latency-exposed at the pipeline's low occupancy, the vector kernel hides them better
+        if (variant == XLB_VARIANT_AUTO && !(half && p.halfway_fraction > 0.01f)) {
+            const int rc = bulk();
             if (rc != -1000) return rc;
         }
     }
     if (vec_ok && variant != XLB_VARIANT_SCALAR) {
-        return has_bc ? launch_vector<T, S, Q, COLL, VMAX, true>(p, st) : launch_vector<T, S, Q, COLL, VMAX, false>(p, st);
+        if (!has_bc) return launch_vector<T, S, Q, COLL, VMAX, false>(p, st);
+        return half ? launch_vector<T, S, Q, COLL, VMAX, true, true>(p, st) : launch_vector<T, S, Q, COLL, VMAX, true, false>(p, st);
     }
     return has_bc ? launch_vector<T, S, Q, COLL, 1, true>(p, st) : launch_vector<T, S, Q, COLL, 1, false>(p, st);
 }

@@ -50,7 +50,9 @@ class IncompressibleNavierStokesStepper(Stepper):
             if not hasattr(force_vector, "shape"):
                 force_vector = np.asarray(force_vector, dtype=np.float64)
             self.collision = ForcedCollision(collision_operator=self.collision, forcing_scheme=forcing_scheme, force_vector=force_vector)
-        self._collision_params = self.collision.abi_params()
+        self._collision_params = self.collision.abi_params() or _lib.XlbCollisionParams()
+        for bc in self.boundary_conditions:  # which BC kinds the kernel has to be able to handle (0 would mean "any")
+            self._collision_params.bc_kind_mask |= 1 << int(bc.abi_kind)
         self.streaming_scheme = streaming_scheme
         if streaming_scheme != "pull":
             raise NotImplementedError(f"Unknown or unimplemented streaming scheme for backend: {self.compute_backend}")  # nse_stepper.py:91-92
@@ -65,6 +67,7 @@ class IncompressibleNavierStokesStepper(Stepper):
         _, f_0, f_1, missing_mask, bc_mask = create_nse_fields(
             grid=self.grid, velocity_set=self.velocity_set, compute_backend=self.compute_backend, precision_policy=self.precision_policy
         )
+        self._collision_params.halfway_fraction = self._halfway_fraction(bc_mask)
         bc_mask, missing_mask = self._process_boundary_conditions(self.boundary_conditions, bc_mask, missing_mask)
         if initializer is not None:
             f_0 = initializer(bc_mask, f_0)
@@ -79,6 +82,20 @@ class IncompressibleNavierStokesStepper(Stepper):
             else:
                 f_0 = initialize_eq(f_0, self.grid, self.velocity_set, self.precision_policy, self.compute_backend)
         return f_0, f_1, bc_mask, missing_mask
+
+    def _halfway_fraction(self, bc_mask):
+        """Share of this block's cells listed by HalfwayBounceBackBC objects (obstacle interiors included): a hint for the
+        kernel-variant choice of ``xlb_step_ex`` (``XlbCollisionParams.halfway_fraction``)."""
+        n = 0
+        x0 = getattr(self.grid, "x_offset", 0)
+        nx_local = self.grid.shape[0]
+        for bc in self.boundary_conditions:
+            idx = getattr(bc, "indices", None)
+            if idx is None or int(bc.abi_kind) != _lib.BC_HALFWAY:
+                continue
+            xs = np.asarray(idx[0] if not isinstance(idx, torch.Tensor) else idx[0].cpu())
+            n += int(np.count_nonzero((xs >= x0) & (xs < x0 + nx_local))) if getattr(self.grid, "halo", 0) else int(xs.size)
+        return n / max(1, bc_mask.numel())
 
     def _process_boundary_conditions(self, boundary_conditions, bc_mask, missing_mask):
         check_bc_overlaps(boundary_conditions, self.velocity_set.d, self.compute_backend)
