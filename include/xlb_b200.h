@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define XLB_B200_ABI_VERSION 2
+#define XLB_B200_ABI_VERSION 3
 
 /* element types (xlb/precision_policy.py:13-54) */
 enum { XLB_F16 = 0, XLB_F32 = 1, XLB_F64 = 2, XLB_U8 = 3 };
@@ -81,6 +81,11 @@ typedef struct XlbCollisionParams {
     double force[3];         /* force_vector in KERNEL axes (a 2-D force (Fx, Fy) is passed as (0, Fx, Fy)) */
     double halfway_fraction; /* hint: fraction of the block's cells tagged with a HalfwayBounceBackBC (obstacle interiors
                                 included); 0 = unknown / none.  Only steers the choice between kernel variants */
+    const int64_t* bc_cells; /* optional device list (see xlb_list_bc_cells) of the linear indices, inside planes [x_begin, x_end),
+                                of the cells whose BC kind needs the per-cell engine (DoNothing, Zou-He, regularized, extrapolation
+                                outflow).  When given, the fused kernel leaves those cells to a second, dense launch over the list
+                                instead of diverging into the per-cell engine; NULL = handle them inside the fused kernel */
+    int64_t n_bc_cells;      /* entries of bc_cells */
 } XlbCollisionParams;
 
 const char* xlb_last_error(void);
@@ -102,6 +107,14 @@ int xlb_step(const XlbDomain* dom, int collision, const void* f0, void* f1, cons
 int xlb_step_ex(const XlbDomain* dom, int collision, const XlbCollisionParams* cp, const void* f0, void* f1, const uint8_t* bc_mask,
                 const uint8_t* missing_mask, const XlbBcEntry* bc_table, int n_bc, double omega, int timestep, int x_begin, int x_end,
                 int variant, void* stream);
+
+/* Compacts the cells of planes [x_begin, x_end) whose bc id maps to a kind in ``kind_mask`` (OR of 1 << XLB_BC_*; 0 = the kinds
+ * XlbCollisionParams.bc_cells is meant for) into ``cells`` (linear indices (x*ny + y)*nz + z in no particular order, capacity ``capacity``
+ * entries; sort them for coalesced access) and adds the number found to ``*count`` (device pointer, int64, zero it first; it may exceed ``capacity``, in which case only
+ * the first ``capacity`` slots were written -- call again with a larger buffer).  cells == NULL only counts.  Setup-time
+ * helper of the stepper (replaces the per-BC kernel specialisation of nse_stepper.py:351-380). */
+int xlb_list_bc_cells(const XlbDomain* dom, const uint8_t* bc_mask, const XlbBcEntry* bc_table, int kind_mask, int x_begin, int x_end,
+                      int64_t* cells, int64_t capacity, int64_t* count, void* stream);
 
 /* Stream.__call__ (stream.py:29-62): f_out[l,x] = f_in[l, x - c_l] periodic. dtype = element type. */
 int xlb_stream(const XlbDomain* dom, int dtype, const void* f_in, void* f_out, void* stream);

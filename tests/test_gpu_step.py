@@ -263,3 +263,95 @@ def test_bulk_variant_many_steps_and_slab_ranges():
         a.launch_range(f_0, f_1, bc_mask, missing, case["omega"], 0, xb, xe)
     b(g_0, g_1, bc_mask, missing, case["omega"], 0)
     assert torch.equal(f_1, g_1)
+
+
+# ----------------------------------------------------------------------------- BC cell list (XlbCollisionParams.bc_cells)
+LIST_CASES = [
+    cases.sphere3d((48, 24, 24)),
+    cases.sphere3d((28, 16, 256)),  # bulk-staged kernel
+    cases.sphere3d((36, 24, 24), outlet="donothing", moving_sphere=(0.01, 0.0, 0.005)),
+    cases.sphere3d((40, 24, 20), lattice="D3Q19", collision="BGK", inlet="regularized_pressure", outlet="pressure"),
+    cases.sphere3d((48, 24, 24), policy="FP32FP16"),
+]
+
+
+def test_list_bc_cells_matches_numpy():
+    """xlb_list_bc_cells: the cells of the listed BC kinds, any order, restricted to an x range."""
+    from ctypes import byref
+
+    case = cases.sphere3d((23, 9, 7))  # ragged: 23*9*7 is not a multiple of 16
+    st, bcs = build_product(case)
+    f_0, _, bc_mask, _ = st.prepare_fields()
+    _, dom, table, _, _, _ = st._get_plan(f_0)
+    listed_ids = [bc.id for bc in bcs if int(bc.abi_kind) in st._LISTED_KINDS]
+    assert listed_ids
+    m = to_np(bc_mask)[0]
+    for xb, xe in [(0, 23), (0, 1), (1, 22), (22, 23), (5, 5)]:
+        sel = np.isin(m, listed_ids)
+        sel[:xb] = False
+        sel[xe:] = False
+        want = np.flatnonzero(sel.reshape(-1))
+        count = torch.zeros(1, dtype=torch.int64, device="cuda")
+        rc = _lib.lib().xlb_list_bc_cells(byref(dom), bc_mask.data_ptr(), table.data_ptr(), 0, xb, xe, None, 0, count.data_ptr(), _lib.current_stream_ptr())
+        _lib.check(rc, "xlb_list_bc_cells")
+        assert int(count.item()) == want.size
+        buf = torch.full((want.size + 3,), -1, dtype=torch.int64, device="cuda")
+        count.zero_()
+        rc = _lib.lib().xlb_list_bc_cells(byref(dom), bc_mask.data_ptr(), table.data_ptr(), 0, xb, xe, buf.data_ptr(), buf.numel(), count.data_ptr(),
+                                          _lib.current_stream_ptr())
+        _lib.check(rc, "xlb_list_bc_cells")
+        got = to_np(buf)
+        assert np.array_equal(np.sort(got[: want.size]), want) and np.all(got[want.size:] == -1)
+    # explicit kind mask: the half-way obstacle only
+    half_ids = [bc.id for bc in bcs if int(bc.abi_kind) == _lib.BC_HALFWAY]
+    count = torch.zeros(1, dtype=torch.int64, device="cuda")
+    rc = _lib.lib().xlb_list_bc_cells(byref(dom), bc_mask.data_ptr(), table.data_ptr(), 1 << _lib.BC_HALFWAY, 0, 23, None, 0, count.data_ptr(),
+                                      _lib.current_stream_ptr())
+    _lib.check(rc, "xlb_list_bc_cells")
+    assert int(count.item()) == int(np.isin(m, half_ids).sum())
+
+
+@pytest.mark.parametrize("case", LIST_CASES, ids=lambda c: c["name"])
+def test_bc_cell_list_path_is_bitwise_identical(case):
+    """Fused kernel + dense launch over the BC cell list == fused kernel with the in-kernel per-cell path, bitwise, over
+    several steps and for x sub-range launches (the multi-GPU schedule)."""
+    a, _ = build_product(case)
+    f_0, f_1, bc_mask, missing = a.prepare_fields()
+    assert a._cells[1] is not None and a._cells[1].numel() > 0
+    b, _ = build_product(case, backend_config={"bc_cell_list": False})
+    g_0, g_1, bc_b, mm_b = b.prepare_fields()
+    assert b._cells[1] is None
+    f_0.copy_(to_dev(cases.random_state(case, seed=3)))
+    g_0.copy_(f_0)
+    n0 = _lib.launch_count()
+    a(f_0, f_1, bc_mask, missing, case["omega"], 0)
+    assert _lib.launch_count() - n0 == 2  # fused kernel + list kernel
+    f_1.zero_()
+    for i in range(6):
+        f_0, f_1 = a(f_0, f_1, bc_mask, missing, case["omega"], i)
+        f_0, f_1 = f_1, f_0
+        g_0, g_1 = b(g_0, g_1, bc_b, mm_b, case["omega"], i)
+        g_0, g_1 = g_1, g_0
+    assert torch.equal(f_0, g_0)
+    nx = case["shape"][0]
+    f_1.zero_()
+    for xb, xe in [(0, 1), (1, nx - 1), (nx - 1, nx)]:
+        a.launch_range(f_0, f_1, bc_mask, missing, case["omega"], 0, xb, xe)
+    b(g_0, g_1, bc_b, mm_b, case["omega"], 0)
+    assert torch.equal(f_1, g_1)
+
+
+def test_bc_cell_list_follows_mask_updates():
+    """The list is cached per bc_mask content: an in-place edit of the mask rebuilds it."""
+    case = cases.sphere3d((48, 24, 24))
+    st, bcs = build_product(case)
+    f_0, f_1, bc_mask, missing = st.prepare_fields()
+    n_before = st._cells[1].numel()
+    outlet = [bc for bc in bcs if int(bc.abi_kind) == _lib.BC_EXTRAPOLATION][0]
+    bc_mask[bc_mask == outlet.id] = 0  # drop the outflow BC (in place -> version bump)
+    st(f_0, f_1, bc_mask, missing, case["omega"], 0)
+    assert st._cells[1].numel() < n_before
+    ref, _ = build_product(case, backend_config={"kernel_variant": _lib.VARIANT_GENERIC})
+    g_1 = torch.zeros_like(f_1)
+    ref(f_0, g_1, bc_mask, missing, case["omega"], 0)
+    assert torch.equal(f_1, g_1)

@@ -10,7 +10,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("XLB_B200_LIB", os.path.join(_HERE, "_lib", "libxlb_b200.so"))
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 # enums of include/xlb_b200.h
 BGK, KBC, SMAGORINSKY_LES_BGK = 0, 1, 2
@@ -42,6 +42,8 @@ class XlbCollisionParams(Structure):
         ("bc_kind_mask", c_int32),
         ("force", c_double * 3),
         ("halfway_fraction", c_double),
+        ("bc_cells", c_void_p),
+        ("n_bc_cells", c_int64),
     ]
 
 
@@ -80,6 +82,7 @@ EXPORTS = {
     "xlb_launch_count": (c_longlong, []),
     "xlb_step": (c_int, [POINTER(XlbDomain), c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_double, c_int, c_int, c_int, c_int, c_void_p]),
     "xlb_step_ex": (c_int, [POINTER(XlbDomain), c_int, POINTER(XlbCollisionParams), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_double, c_int, c_int, c_int, c_int, c_void_p]),
+    "xlb_list_bc_cells": (c_int, [POINTER(XlbDomain), c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p]),
     "xlb_stream": (c_int, [POINTER(XlbDomain), c_int, c_void_p, c_void_p, c_void_p]),
     "xlb_macroscopic": (c_int, [POINTER(XlbDomain), c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     "xlb_second_moment": (c_int, [POINTER(XlbDomain), c_int, c_void_p, c_int, c_void_p, c_void_p]),

@@ -116,6 +116,11 @@ int xlb_step_ex(const XlbDomain* dom, int collision, const XlbCollisionParams* c
     p.omega = omega;
     p.bc_kind_mask = cp ? cp->bc_kind_mask : 0;
     p.halfway_fraction = cp ? (float)cp->halfway_fraction : 0.f;
+    if (cp && cp->bc_cells) {
+        if (cp->n_bc_cells < 0 || cp->n_bc_cells >= (1ll << 37)) return set_error(XLB_EINVAL, "xlb_step: bad n_bc_cells");
+        p.cells = reinterpret_cast<const long long*>(cp->bc_cells);
+        p.n_cells = cp->n_bc_cells;
+    }
     if (collision != XLB_BGK && collision != XLB_KBC && collision != XLB_SMAGORINSKY_LES_BGK)
         return set_error(XLB_EINVAL, "xlb_step: unknown collision model");
     if (collision == XLB_SMAGORINSKY_LES_BGK) {
@@ -335,6 +340,32 @@ int xlb_mask_missing(const XlbDomain* dom, const uint8_t* solid, const int32_t o
     if (dom->q == 9) mask_missing_kernel<9><<<nb, 256, 0, st>>>(p);
     else if (dom->q == 19) mask_missing_kernel<19><<<nb, 256, 0, st>>>(p);
     else mask_missing_kernel<27><<<nb, 256, 0, st>>>(p);
+    return count_launch(cudaGetLastError());
+}
+
+int xlb_list_bc_cells(const XlbDomain* dom, const uint8_t* bc_mask, const XlbBcEntry* bc_table, int kind_mask, int x_begin, int x_end,
+                      int64_t* cells, int64_t capacity, int64_t* count, void* stream) {
+    if (int rc = check_domain(dom, "xlb_list_bc_cells")) return rc;
+    if (!bc_mask || !bc_table || !count) return set_error(XLB_EINVAL, "xlb_list_bc_cells: null pointer");
+    if (x_begin < 0 || x_end > dom->nx || x_begin > x_end) return set_error(XLB_EINVAL, "xlb_list_bc_cells: bad x range");
+    if (capacity < 0 || (cells == nullptr && capacity != 0)) return set_error(XLB_EINVAL, "xlb_list_bc_cells: bad capacity");
+    if (reinterpret_cast<uintptr_t>(bc_mask) % 16 != 0) return set_error(XLB_EALIGN, "xlb_list_bc_cells: bc_mask must be 16-byte aligned");
+    if (x_begin == x_end) return 0;
+    ListParams p;
+    std::memset(&p, 0, sizeof(p));
+    const long long plane = (long long)dom->ny * dom->nz;
+    p.bc_mask = bc_mask;
+    p.bct = bc_table;
+    p.first = x_begin * plane;
+    p.last = x_end * plane;
+    p.ncell = dom->nx * plane;
+    p.kind_mask = kind_mask ? kind_mask : XLB_BC_LISTED_KINDS;
+    p.cells = reinterpret_cast<long long*>(cells);
+    p.capacity = capacity;
+    p.count = reinterpret_cast<unsigned long long*>(count);
+    const long long span = p.last - (p.first & ~15ll);
+    const long long nthreads = (span + 15) / 16;
+    list_bc_cells_kernel<<<blocks_for(nthreads, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(p);
     return count_launch(cudaGetLastError());
 }
 

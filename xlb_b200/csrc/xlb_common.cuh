@@ -180,6 +180,8 @@ struct StepParams {
     int bc_kind_mask;  // bit k set: a BC of kind k may be present (0 = unknown, assume any)
     double les_c;      // 36 * smagorinsky_coef^2 (smagorinsky_les_bgk.py:62)
     double force3[3];  // 3 * force_vector, kernel axes (exact_difference_force.py:72-75)
+    const long long* cells;  // XlbCollisionParams.bc_cells: cells of listed BC kinds, updated by step_cells_kernel
+    long long n_cells;
 };
 
 // collision template codes: low bits = model (XLB_BGK / XLB_KBC / XLB_SMAGORINSKY_LES_BGK), bit 2 = exact-difference force
@@ -187,5 +189,11 @@ struct StepParams {
 #define XLB_COLL_MODEL(COLL) ((COLL) & 3)
 
 XLB_HD bool bc_is_complex(int kind) { return kind >= XLB_BC_HALFWAY; }
+// kinds that go on the BC cell list (XlbCollisionParams.bc_cells): every complex kind except the half-way bounce-back,
+// whose cells fill obstacle volumes and have their own vectorised in-register path
+XLB_HD bool bc_is_listed(int kind) { return kind >= XLB_BC_DONOTHING; }
+#define XLB_BC_LISTED_KINDS                                                                                                      \
+    ((1 << XLB_BC_DONOTHING) | (1 << XLB_BC_ZOUHE_VELOCITY) | (1 << XLB_BC_ZOUHE_PRESSURE) | (1 << XLB_BC_EXTRAPOLATION) | \
+     (1 << XLB_BC_REGULARIZED_VELOCITY) | (1 << XLB_BC_REGULARIZED_PRESSURE))
 
 }  // namespace xlb

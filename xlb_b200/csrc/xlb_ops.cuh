@@ -364,4 +364,64 @@ __global__ void __launch_bounds__(256) mask_missing_kernel(const __grid_constant
     });
 }
 
+// ------------------------------------------------------------------ BC cell list (XlbCollisionParams.bc_cells)
+struct ListParams {
+    const uint8_t* bc_mask;
+    const XlbBcEntry* bct;
+    long long first, last;  // linear cell range [first, last)
+    long long ncell;        // cells of the whole block (bytes of bc_mask)
+    int kind_mask;
+    long long* cells;
+    long long capacity;
+    unsigned long long* count;
+};
+
+// one thread per 16 cells (one 128-bit load of bc ids); hits are appended with one atomic per warp
+__global__ void __launch_bounds__(256) list_bc_cells_kernel(const __grid_constant__ ListParams p) {
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long c0 = (p.first & ~15ll) + t * 16;  // bc_mask rows are 16-byte aligned (checked on the host)
+    uint32_t hit = 0;
+    if (c0 < p.last) {
+        uint4 w = make_uint4(0, 0, 0, 0);
+        if (c0 + 16 <= p.ncell) {
+            w = *reinterpret_cast<const uint4*>(p.bc_mask + c0);
+        } else {  // ragged end of the block
+            uint32_t tail[4] = {0, 0, 0, 0};
+            for (int j = 0; c0 + j < p.ncell; ++j) tail[j >> 2] |= (uint32_t)p.bc_mask[c0 + j] << (8 * (j & 3));
+            w = make_uint4(tail[0], tail[1], tail[2], tail[3]);
+        }
+        const uint32_t words[4] = {w.x, w.y, w.z, w.w};
+        if (w.x | w.y | w.z | w.w) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                const int id = (words[j >> 2] >> (8 * (j & 3))) & 0xff;
+                const long long c = c0 + j;
+                if (id != 0 && c >= p.first && c < p.last && ((p.kind_mask >> p.bct[id].kind) & 1)) hit |= 1u << j;
+            }
+        }
+    }
+    const int n = __popc(hit);
+    // warp-aggregated append: exclusive prefix of n over the lanes, one atomicAdd by the last lane
+    const int lane = threadIdx.x & 31;
+    int incl = n;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += v;
+    }
+    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    if (total == 0) return;
+    unsigned long long base = 0;
+    if (lane == 31) base = atomicAdd(p.count, (unsigned long long)total);
+    base = __shfl_sync(0xffffffffu, base, 31);
+    long long slot = (long long)base + (incl - n);
+    if (p.cells == nullptr) return;
+    while (hit) {
+        const int j = __ffs(hit) - 1;
+        hit &= hit - 1;
+        if (slot < p.capacity) p.cells[slot] = c0 + j;
+        ++slot;
+    }
+}
+
 }  // namespace xlb

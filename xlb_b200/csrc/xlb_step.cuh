@@ -117,6 +117,23 @@ __global__ void __launch_bounds__(128) step_generic_kernel(const __grid_constant
     cell_update_generic<T, S, Q, COLL>(p, x, (int)(i / p.nz), (int)(i % p.nz));
 }
 
+// the cells of the BC cell list (XlbCollisionParams.bc_cells) through the generic engine: consecutive threads take
+// consecutive list entries, so a sorted list of a boundary plane is read and written coalesced, at full occupancy.
+// Runs after the fused kernel on the same stream and overwrites what that kernel's fast path stored for these cells;
+// the engine reads f0 only, so the order between the two launches does not change the result.
+template <typename T, typename S, int Q, int COLL>
+__global__ void __launch_bounds__(128) step_cells_kernel(const __grid_constant__ StepParams p) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= p.n_cells) return;
+    const long long cell = p.cells[i];
+    const long long plane = (long long)p.ny * p.nz;
+    const int x = (int)(cell / plane);
+    const int r = (int)(cell - x * plane);
+    const int y = r / p.nz;
+    if (x < p.x_begin || x >= p.x_end) return;
+    cell_update_generic<T, S, Q, COLL>(p, x, y, r - y * p.nz);
+}
+
 // ------------------------------------------------------------------ fused vector kernel (K1)
 // predicated scalar load (no branch): returns *ptr where pred, else keep
 XLB_D float ld_if(const float* ptr, bool pred, float keep) {
@@ -178,12 +195,14 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_c
                     const int k = p.bct[ids[j]].kind;
                     k_full[j] = k == XLB_BC_FULLWAY;
                     k_eq[j] = k == XLB_BC_EQUILIBRIUM;
+                    // listed kinds are left to step_cells_kernel when the caller passed the BC cell list
+                    const bool here = p.cells == nullptr || !bc_is_listed(k);
                     if constexpr (HALF) {
                         k_half[j] = k == XLB_BC_HALFWAY;
                         any_half |= k_half[j];
-                        slow |= bc_is_complex(k) && !k_half[j];
+                        slow |= bc_is_complex(k) && !k_half[j] && here;
                     } else {
-                        slow |= bc_is_complex(k);
+                        slow |= bc_is_complex(k) && here;
                     }
                 }
             }

@@ -192,12 +192,13 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
                     const int k = p.bct[ids[j]].kind;
                     k_full[j] = k == XLB_BC_FULLWAY;
                     k_eq[j] = k == XLB_BC_EQUILIBRIUM;
-                    if constexpr (HALF) {  // see step_vector_kernel
+                    const bool here = p.cells == nullptr || !bc_is_listed(k);  // see step_vector_kernel
+                    if constexpr (HALF) {
                         k_half[j] = k == XLB_BC_HALFWAY;
                         any_half |= k_half[j];
-                        slow |= bc_is_complex(k) && !k_half[j];
+                        slow |= bc_is_complex(k) && !k_half[j] && here;
                     } else {
-                        slow |= bc_is_complex(k);
+                        slow |= bc_is_complex(k) && here;
                     }
                 }
             }

@@ -104,7 +104,22 @@ static int launch_generic(const StepParams& p, cudaStream_t st) {
 }
 
 template <typename T, typename S, int Q, int COLL>
-static int step_coll(const StepParams& p, int variant, cudaStream_t st) {
+static int step_main(const StepParams& p, int variant, cudaStream_t st);
+
+// the fused kernel, then (when the caller passed XlbCollisionParams.bc_cells) the dense launch over the BC cell list
+template <typename T, typename S, int Q, int COLL>
+static int step_coll(const StepParams& p0, int variant, cudaStream_t st) {
+    StepParams p = p0;
+    const bool has_bc = p.bc_mask != nullptr && p.bct != nullptr;
+    if (!has_bc || variant == XLB_VARIANT_GENERIC || p.n_cells <= 0) p.cells = nullptr;
+    if (int rc = step_main<T, S, Q, COLL>(p, variant, st)) return rc;
+    if (p.cells == nullptr) return 0;
+    step_cells_kernel<T, S, Q, COLL><<<(unsigned)((p.n_cells + 127) / 128), 128, 0, st>>>(p);
+    return count_launch(cudaGetLastError());
+}
+
+template <typename T, typename S, int Q, int COLL>
+static int step_main(const StepParams& p, int variant, cudaStream_t st) {
 #ifdef XLB_TUNE_V
     constexpr int VMAX = XLB_TUNE_V;
 #else

@@ -61,6 +61,9 @@ class IncompressibleNavierStokesStepper(Stepper):
         self.macroscopic = Macroscopic(self.velocity_set, self.precision_policy, self.compute_backend)
         self.kernel_variant = int(self.backend_config.get("kernel_variant", _lib.VARIANT_AUTO)) if self.backend_config else _lib.VARIANT_AUTO
         self._plan = None  # (key, domain struct, bc table tensor, n_bc)
+        # BC cell list (XlbCollisionParams.bc_cells): (key, sorted cell indices on the device, per-plane offsets on the host)
+        self._cells = None
+        self._use_cell_list = bool(self.backend_config.get("bc_cell_list", True)) if self.backend_config else True
 
     # ------------------------------------------------------------------ setup (nse_stepper.py:99-205)
     def prepare_fields(self, initializer=None):
@@ -81,6 +84,8 @@ class IncompressibleNavierStokesStepper(Stepper):
                     f_0[l].fill_(float(w[l]))
             else:
                 f_0 = initialize_eq(f_0, self.grid, self.velocity_set, self.precision_policy, self.compute_backend)
+        if self.boundary_conditions:
+            self._bc_cell_list(f_0, bc_mask)  # built here so that the step loop itself never synchronises
         return f_0, f_1, bc_mask, missing_mask
 
     def _halfway_fraction(self, bc_mask):
@@ -135,6 +140,38 @@ class IncompressibleNavierStokesStepper(Stepper):
             self._plan = (key, dom, table, n_bc, x_begin, x_end)
         return self._plan
 
+    _LISTED_KINDS = (_lib.BC_DONOTHING, _lib.BC_ZOUHE_VELOCITY, _lib.BC_ZOUHE_PRESSURE, _lib.BC_EXTRAPOLATION,
+                     _lib.BC_REGULARIZED_VELOCITY, _lib.BC_REGULARIZED_PRESSURE)
+
+    def _bc_cell_list(self, f_0, bc_mask):
+        """Sorted device list of the cells whose BC kind needs the per-cell engine (Zou-He, regularized, extrapolation
+        outflow, do-nothing) plus its per-plane offsets, cached per ``bc_mask`` content.  ``xlb_step_ex`` then updates
+        those cells with one dense launch over the list instead of diverging inside the fused kernel.  The reference
+        specialises its kernel per BC list at construction (nse_stepper.py:351-380); this is the analogous setup step."""
+        key = (bc_mask.data_ptr(), bc_mask._version, tuple(bc_mask.shape))
+        if self._cells is not None and self._cells[0] == key:
+            return self._cells
+        self._cells = (key, None, None)
+        listed = any(int(bc.abi_kind) in self._LISTED_KINDS for bc in self.boundary_conditions)
+        if not (self._use_cell_list and listed) or bc_mask.data_ptr() % 16 != 0:
+            return self._cells
+        _, dom, table, n_bc, _, _ = self._get_plan(f_0)
+        count = torch.zeros(1, dtype=torch.int64, device=bc_mask.device)
+        args = (byref(dom), bc_mask.data_ptr(), table.data_ptr(), 0, 0, int(dom.nx))
+        check(lib().xlb_list_bc_cells(*args, None, 0, count.data_ptr(), stream_ptr()), "IncompressibleNavierStokesStepper")
+        n = int(count.item())
+        if n == 0:
+            return self._cells
+        cells = torch.empty(n, dtype=torch.int64, device=bc_mask.device)
+        count.zero_()
+        check(lib().xlb_list_bc_cells(*args, cells.data_ptr(), n, count.data_ptr(), stream_ptr()), "IncompressibleNavierStokesStepper")
+        cells = torch.sort(cells).values
+        plane = int(dom.ny) * int(dom.nz)
+        edges = torch.arange(int(dom.nx) + 1, dtype=torch.int64, device=bc_mask.device) * plane
+        offsets = torch.searchsorted(cells, edges).cpu().tolist()
+        self._cells = (key, cells, offsets)
+        return self._cells
+
     # ------------------------------------------------------------------ the step
     def launch_range(self, f_0, f_1, bc_mask, missing_mask, omega, timestep, x_begin, x_end):
         """One ``xlb_step`` launch that updates planes ``[x_begin, x_end)`` of ``f_1`` (local plane indices, ghost
@@ -152,6 +189,13 @@ class IncompressibleNavierStokesStepper(Stepper):
             self._check_field(bc_mask, "bc_mask", 1)
             self._check_field(missing_mask, "missing_mask", q)
         cp = self._collision_params
+        cp.bc_cells, cp.n_bc_cells = None, 0
+        if n_bc:
+            _, cells, offsets = self._bc_cell_list(f_0, bc_mask)
+            if cells is not None:
+                lo, hi = offsets[int(x_begin)], offsets[int(x_end)]
+                if hi > lo:
+                    cp.bc_cells, cp.n_bc_cells = cells.data_ptr() + 8 * lo, hi - lo
         rc = lib().xlb_step_ex(
             byref(dom), self.collision.abi_model, byref(cp) if cp is not None else None, f_0.data_ptr(), f_1.data_ptr(),
             bc_mask.data_ptr() if n_bc else None, missing_mask.data_ptr() if n_bc else None, table.data_ptr() if n_bc else None, n_bc,
