@@ -374,6 +374,7 @@ def run_native(args):
             "bytes_per_cell": b_alg(vs.q, policy),
             "cells_per_launch": ncell,
             "kernel_ms": k_ms,
+            "launches_per_step": launches / max(1, args.steps),  # 2 = fused kernel + dense launch over the BC cell list
             "peak_source": peak_src,
         }
 

@@ -154,6 +154,17 @@ int xlb_mask_tag(const XlbDomain* dom, const int32_t* indices, int64_t n, const 
 int xlb_mask_missing(const XlbDomain* dom, const uint8_t* solid, const int32_t origin[3], const int32_t global_shape[3],
                      uint8_t* missing_mask, void* stream);
 
+/* MeshMaskerRay (boundary_masker/ray.py:43-77) + resolve_out_of_bound_kernel (mesh_boundary_masker.py:157-179): voxelises a triangle
+ * soup (``triangles`` = float32 [n_triangles][3 vertices][3 coords], lattice units, GLOBAL kernel-axis coordinates, device
+ * pointer).  Every cell of the local block from whose centre a lattice ray of length |c_l| hits the surface gets
+ * bc_mask = id and missing_mask[opp l] = 1; cells tagged with ``id`` on the domain edge also get the directions that
+ * pull from outside the global domain.  ``distance_keys`` (optional, uint64 [q][N], initialised to all ones) receives per
+ * (direction, cell) the closest hit as (bits of t) << 32 | (bits of |hit - centre| / |c_l|), both FP32 (ray.py:72-76).
+ * The BVH query of the reference (warp.mesh_query_ray) is replaced by one warp per triangle over the cells of its grown
+ * bounding box with the watertight ray/triangle test (Woop, Benthin, Wald 2013); 3-D lattices only. */
+int xlb_mask_mesh_ray(const XlbDomain* dom, const float* triangles, int64_t n_triangles, const int32_t origin[3],
+                      const int32_t global_shape[3], int id, uint8_t* bc_mask, uint8_t* missing_mask, uint64_t* distance_keys, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -9,7 +9,7 @@ import sys
 import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-EXAMPLES = ["mlups_3d.py", "flow_past_sphere_3d.py"]
+EXAMPLES = ["mlups_3d.py", "flow_past_sphere_3d.py", "windtunnel_3d.py"]
 
 
 @pytest.mark.parametrize("name", EXAMPLES)
@@ -34,3 +34,22 @@ def test_sphere_example_reports_positive_drag():
     last = [ln for ln in r.stdout.splitlines() if ln.startswith("step ")][-1]
     cd = float(last.split("CD=")[1].split()[0])
     assert 0.0 < cd < 50.0, last  # the flow pushes the sphere downstream
+
+
+@pytest.mark.gpu
+def test_windtunnel_example_with_mesh_obstacle(tmp_path):
+    """Mesh obstacle read from an STL file, voxelised by the ray-cast masker; the drag on it is positive."""
+    sys.path.insert(0, ROOT)
+    from xlb_b200.helper import ellipsoid_soup, write_stl
+
+    stl = str(tmp_path / "body.stl")
+    write_stl(stl, ellipsoid_soup(radii=(2.0, 1.0, 0.8), subdivisions=3))
+    r = subprocess.run(
+        [sys.executable, os.path.join(ROOT, "examples", "windtunnel_3d.py"), "--shape", "128", "48", "48", "--steps", "300", "--interval", "150", "--stl", stl],
+        capture_output=True, text=True, timeout=600,
+    )
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "boundary cells" in r.stdout
+    last = [ln for ln in r.stdout.splitlines() if ln.startswith("step ")][-1]
+    cd = float(last.split("CD=")[1].split()[0])
+    assert 0.0 < cd < 50.0, last

@@ -315,7 +315,7 @@ def test_list_bc_cells_matches_numpy():
 def test_bc_cell_list_path_is_bitwise_identical(case):
     """Fused kernel + dense launch over the BC cell list == fused kernel with the in-kernel per-cell path, bitwise, over
     several steps and for x sub-range launches (the multi-GPU schedule)."""
-    a, _ = build_product(case)
+    a, _ = build_product(case, backend_config={"bc_cell_list": True})
     f_0, f_1, bc_mask, missing = a.prepare_fields()
     assert a._cells[1] is not None and a._cells[1].numel() > 0
     b, _ = build_product(case, backend_config={"bc_cell_list": False})
@@ -339,12 +339,15 @@ def test_bc_cell_list_path_is_bitwise_identical(case):
         a.launch_range(f_0, f_1, bc_mask, missing, case["omega"], 0, xb, xe)
     b(g_0, g_1, bc_b, mm_b, case["omega"], 0)
     assert torch.equal(f_1, g_1)
+    c, _ = build_product(case)  # default "auto": this block is far too small for the second launch to pay off
+    c.prepare_fields()
+    assert c._cells[1] is None
 
 
 def test_bc_cell_list_follows_mask_updates():
     """The list is cached per bc_mask content: an in-place edit of the mask rebuilds it."""
     case = cases.sphere3d((48, 24, 24))
-    st, bcs = build_product(case)
+    st, bcs = build_product(case, backend_config={"bc_cell_list": True})
     f_0, f_1, bc_mask, missing = st.prepare_fields()
     n_before = st._cells[1].numel()
     outlet = [bc for bc in bcs if int(bc.abi_kind) == _lib.BC_EXTRAPOLATION][0]
@@ -355,3 +358,28 @@ def test_bc_cell_list_follows_mask_updates():
     g_1 = torch.zeros_like(f_1)
     ref(f_0, g_1, bc_mask, missing, case["omega"], 0)
     assert torch.equal(f_1, g_1)
+
+
+# ----------------------------------------------------------------------------- FP16 storage: packed half2 kernel
+H2_CASES = [
+    cases.cavity3d(16, policy="FP32FP16", omega=1.7),
+    cases.cavity3d(0, shape=(6, 10, 20), policy="FP32FP16", omega=1.3),  # ntz = 5: not a power of two, ragged warps
+    cases.periodic((8, 6, 128), policy="FP32FP16"),  # full warps along z: shuffles carry the z shift
+    cases.sphere3d((48, 24, 24), policy="FP32FP16"),  # D3Q27 KBC, half-way obstacle (vectorised path) + complex BCs
+    cases.sphere3d((40, 24, 20), lattice="D3Q19", collision="BGK", policy="FP32FP16", inlet="pressure", outlet="pressure"),
+    cases.sphere3d((36, 24, 24), policy="FP32FP16", outlet="donothing", moving_sphere=(0.01, 0.0, 0.005)),
+    cases.cavity3d(16, policy="FP32FP16", omega=1.9, collision="SmagorinskyLESBGK"),
+    cases.cavity3d(16, policy="FP32FP16", omega=1.7, force=(1e-4, 2e-5, 0.0)),  # forced: widened path
+    cases.cavity2d(24, policy="FP32FP16", collision="KBC"),
+]
+
+
+@pytest.mark.parametrize("case", H2_CASES, ids=lambda c: c["name"])
+def test_fp16_packed_kernel_bitwise_equals_generic(case):
+    """step_vector_h2_kernel (populations packed as half2 from load to store, pair-wise widening) performs the same FP32
+    arithmetic and the same round-to-nearest-even store as the per-cell generic kernel."""
+    a, ref = _one_step(case, _lib.VARIANT_VECTOR, seed=11)
+    b, _ = _one_step(case, _lib.VARIANT_GENERIC, seed=11)
+    assert a.dtype == np.float16
+    assert np.array_equal(a.view(np.uint16), b.view(np.uint16))
+    assert rel_err(a, ref) <= TOL_ONE_STEP["FP32FP16"] * (4 if case["collision"] == "KBC" else 1)

@@ -36,7 +36,7 @@ def build(instance, variants):
 def run(workload, steps, only="", variant=0):
     rows = []
     for lib in sorted(glob.glob(os.path.join(SWEEP_DIR, f"lib_{only}*.so"))):
-        env = dict(os.environ, XLB_B200_LIB=lib)
+        env = dict(os.environ, XLB_B200_LIB=lib, XLB_B200_TUNING_LIB="1")
         r = subprocess.run(
             [sys.executable, os.path.join(ROOT, "bench.py"), "--workload", workload, "--steps", str(steps), "--warmup", "3", "--no-e2e", "--no-cpu-baseline", "--variant", str(variant)],
             env=env, capture_output=True, text=True,

@@ -93,6 +93,7 @@ EXPORTS = {
     "xlb_momentum_transfer": (c_int, [POINTER(XlbDomain), c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "xlb_mask_tag": (c_int, [POINTER(XlbDomain), c_void_p, c_int64, POINTER(c_int32), POINTER(c_int32), c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "xlb_mask_missing": (c_int, [POINTER(XlbDomain), c_void_p, POINTER(c_int32), POINTER(c_int32), c_void_p, c_void_p]),
+    "xlb_mask_mesh_ray": (c_int, [POINTER(XlbDomain), c_void_p, c_int64, POINTER(c_int32), POINTER(c_int32), c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
 }
 
 _lib = None
@@ -109,7 +110,10 @@ def lib():
             "(or `python xlb_b200/build.py`).  xlb_b200 has no CPU fallback."
         )
     handle = ctypes.CDLL(LIB_PATH)
+    partial = os.environ.get("XLB_B200_TUNING_LIB") == "1"  # tools/sweep.py: single-instance tuning builds may predate an entry point
     for name, (res, args) in EXPORTS.items():
+        if partial and not hasattr(handle, name):
+            continue
         fn = getattr(handle, name)  # AttributeError = library does not match include/xlb_b200.h
         fn.restype = res
         fn.argtypes = args

@@ -4,6 +4,7 @@
 #include <cstring>
 
 #include "xlb_host.cuh"
+#include "xlb_mesh.cuh"
 #include "xlb_ops.cuh"
 
 namespace xlb {
@@ -366,6 +367,42 @@ int xlb_list_bc_cells(const XlbDomain* dom, const uint8_t* bc_mask, const XlbBcE
     const long long span = p.last - (p.first & ~15ll);
     const long long nthreads = (span + 15) / 16;
     list_bc_cells_kernel<<<blocks_for(nthreads, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(p);
+    return count_launch(cudaGetLastError());
+}
+
+int xlb_mask_mesh_ray(const XlbDomain* dom, const float* triangles, int64_t n_triangles, const int32_t origin[3],
+                      const int32_t global_shape[3], int id, uint8_t* bc_mask, uint8_t* missing_mask, uint64_t* distance_keys, void* stream) {
+    if (int rc = check_domain(dom, "xlb_mask_mesh_ray")) return rc;
+    if (dom->d != 3) return set_error(XLB_EUNSUPPORTED, "xlb_mask_mesh_ray: mesh maskers are 3-D only (mesh_boundary_masker.py:36-39)");
+    if (n_triangles < 0 || id < 1 || id > 255) return set_error(XLB_EINVAL, "xlb_mask_mesh_ray: bad triangle count or id");
+    if (!bc_mask || !missing_mask || (n_triangles > 0 && !triangles)) return set_error(XLB_EINVAL, "xlb_mask_mesh_ray: null pointer");
+    MeshParams p;
+    std::memset(&p, 0, sizeof(p));
+    p.tri = triangles;
+    p.ntri = n_triangles;
+    p.nx = dom->nx;
+    p.ny = dom->ny;
+    p.nz = dom->nz;
+    for (int a = 0; a < 3; ++a) {
+        p.origin[a] = origin ? origin[a] : 0;
+        p.gshape[a] = global_shape ? global_shape[a] : (a == 0 ? dom->nx : (a == 1 ? dom->ny : dom->nz));
+    }
+    p.id = id;
+    p.bc_mask = bc_mask;
+    p.missing = missing_mask;
+    const long long ncell = (long long)dom->nx * dom->ny * dom->nz;
+    p.mqs = dom->mask_q_stride ? dom->mask_q_stride : ncell;
+    p.dist_key = reinterpret_cast<unsigned long long*>(distance_keys);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (n_triangles > 0) {
+        const unsigned nb = blocks_for(n_triangles * 32, 128);
+        if (dom->q == 19) mesh_ray_kernel<19><<<nb, 128, 0, st>>>(p);
+        else mesh_ray_kernel<27><<<nb, 128, 0, st>>>(p);
+        if (int rc = count_launch(cudaGetLastError())) return rc;
+    }
+    const unsigned nb2 = blocks_for(ncell, 256);
+    if (dom->q == 19) mesh_resolve_oob_kernel<19><<<nb2, 256, 0, st>>>(p);
+    else mesh_resolve_oob_kernel<27><<<nb2, 256, 0, st>>>(p);
     return count_launch(cudaGetLastError());
 }
 

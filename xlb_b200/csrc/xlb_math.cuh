@@ -223,6 +223,49 @@ XLB_D void col_set(T (&f)[Q][V], int l, int J, N x) {
     }
 }
 
+// swap the populations l and o of column J (one lane of a packed pair)
+template <typename T, int Q, int V>
+XLB_D void col_swap(T (&f)[Q][V], int l, int o, int J) {
+    const T t = f[l][J];
+    f[l][J] = f[o][J];
+    f[o][J] = t;
+}
+
+// FP16-stored populations kept packed: word w[l][J/2] holds cells J (low half) and J+1 (high half) of population l.
+// col_get widens a pair to FP32 on access, col_set narrows with round-to-nearest-even (cvt.rn.f16x2.f32, the store
+// rounding of precision_policy.py:105-110) -- so a collision may run on this storage only if it sets every element
+// exactly once, after its last read (BGK / LES / KBC without the forcing pass).
+template <int Q, int W>
+struct PackedH2 {
+    uint32_t w[Q][W];
+};
+XLB_D float2 h2_to_f2(uint32_t w) {
+    __half2 h;
+    *reinterpret_cast<uint32_t*>(&h) = w;
+    return __half22float2(h);
+}
+XLB_D uint32_t f2_to_h2(float a, float b) {
+    const __half2 h = __floats2half2_rn(a, b);
+    return *reinterpret_cast<const uint32_t*>(&h);
+}
+template <typename N, int Q, int W>
+XLB_D N col_get(const PackedH2<Q, W>& f, int l, int J) {
+    static_assert(Num<N>::lanes == 2, "packed fp16 storage is read one pair at a time");
+    return N{h2_to_f2(f.w[l][J >> 1])};
+}
+template <typename N, int Q, int W>
+XLB_D void col_set(PackedH2<Q, W>& f, int l, int J, N x) {
+    static_assert(Num<N>::lanes == 2, "packed fp16 storage is written one pair at a time");
+    f.w[l][J >> 1] = f2_to_h2(x.v.x, x.v.y);
+}
+template <int Q, int W>
+XLB_D void col_swap(PackedH2<Q, W>& f, int l, int o, int J) {
+    const uint32_t a = f.w[l][J >> 1], b = f.w[o][J >> 1];
+    const uint32_t sel = (J & 1) ? 0x7610u : 0x3254u;  // take the other word's high / low half
+    f.w[l][J >> 1] = __byte_perm(a, b, sel);
+    f.w[o][J >> 1] = __byte_perm(b, a, sel);
+}
+
 // weight class of direction L (0 rest, 1 axis, 2 face diagonal, 3 cube diagonal)
 template <int Q, int L>
 XLB_HD constexpr int wclass() {
@@ -296,8 +339,8 @@ XLB_D CollArgs<T> coll_args(const StepParams& p) {
     return a;
 }
 
-template <typename N, typename T, int Q, int COLL, int V, int J>
-XLB_D void collide_cols(T (&f)[Q][V], const CollArgs<T>& ca, const bool* fullway, bool any_fullway) {
+template <typename N, typename T, int Q, int COLL, int V, int J, typename FS>
+XLB_D void collide_cols(FS& f, const CollArgs<T>& ca, const bool* fullway, bool any_fullway) {
     using S = typename Num<N>::scalar;
     constexpr int LN = Num<N>::lanes;
     constexpr int MODEL = XLB_COLL_MODEL(COLL);
@@ -310,11 +353,7 @@ XLB_D void collide_cols(T (&f)[Q][V], const CollArgs<T>& ca, const bool* fullway
                 static_for<Q>([&](auto lc) {
                     XLB_IDX(l, lc);
                     constexpr int o = Dir<Q, l>::o;
-                    if (o > l) {
-                        const T t = f[l][J + k];
-                        f[l][J + k] = f[o][J + k];
-                        f[o][J + k] = t;
-                    }
+                    if (o > l) col_swap(f, l, o, J + k);
                 });
             }
         }

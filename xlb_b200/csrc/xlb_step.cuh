@@ -24,9 +24,13 @@
 namespace xlb {
 
 XLB_D int wrap1(int v, int n) { return v < 0 ? v + n : (v >= n ? v - n : v); }
-XLB_D int wrapn(int v, int n) {
-    v %= n;
-    return v < 0 ? v + n : v;
+XLB_D int wrapn(int v, int n) {  // periodic wrap of an index that is at most a few cells outside [0, n)
+    v = v < 0 ? v + n : (v >= n ? v - n : v);
+    if ((unsigned)v >= (unsigned)n) {  // extents of 1 or 2 cells: general modulo (integer division is slow, keep it off the common path)
+        v %= n;
+        v = v < 0 ? v + n : v;
+    }
+    return v;
 }
 
 // ------------------------------------------------------------------ generic per-cell engine

@@ -4,12 +4,17 @@
 #include "xlb_host.cuh"
 #include "xlb_step.cuh"
 #include "xlb_step_bulk.cuh"
+#include "xlb_step_h2.cuh"
 
 #ifndef XLB_Q
 #error "compile with -DXLB_Q -DXLB_TC -DXLB_TS -DXLB_TAG"
 #endif
 
 // tuning knobs (overridable from the command line for sweeps; see tools/sweep.py)
+// 1: FP32-compute / FP16-store instances run step_vector_h2_kernel (populations packed as half2 from load to store)
+#ifndef XLB_TUNE_H2
+#define XLB_TUNE_H2 1
+#endif
 #ifndef XLB_TUNE_BLOCK
 #define XLB_TUNE_BLOCK 128
 #endif
@@ -36,7 +41,11 @@ static int launch_vector(const StepParams& p0, cudaStream_t st) {
 #else
     constexpr int MINB = (V == 1) ? 4 : default_minb<S, Q>();
 #endif
-    step_vector_kernel<T, S, Q, COLL, V, BLOCK, MINB, HAS_BC, HALF><<<grid, BLOCK, 0, st>>>(p);
+    if constexpr (XLB_TUNE_H2 && std::is_same<S, __half>::value && std::is_same<T, float>::value && V >= 2) {
+        step_vector_h2_kernel<Q, COLL, V, BLOCK, MINB, HAS_BC, HALF><<<grid, BLOCK, 0, st>>>(p);
+    } else {
+        step_vector_kernel<T, S, Q, COLL, V, BLOCK, MINB, HAS_BC, HALF><<<grid, BLOCK, 0, st>>>(p);
+    }
     return count_launch(cudaGetLastError());
 }
 

@@ -47,10 +47,8 @@ class BoundaryCondition(Operator):
         precision_policy = precision_policy or DefaultConfig.default_precision_policy
         compute_backend = compute_backend or DefaultConfig.default_backend
         super().__init__(velocity_set, precision_policy, compute_backend)
-        if mesh_vertices is not None:
-            raise NotImplementedError("mesh-based boundary conditions are outside the scope of the CUDA backend (no JAX path in the reference either)")
         self.indices = indices
-        self.mesh_vertices = None
+        self.mesh_vertices = mesh_vertices  # (N, 3) triangle soup in lattice units, voxelised by MeshMaskerRay (boundary_condition.py:76)
         self.voxelization_method = voxelization_method
         self.implementation_step = implementation_step
         # flags of the reference API (boundary_condition.py:84-105)

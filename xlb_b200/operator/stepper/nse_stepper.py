@@ -63,7 +63,10 @@ class IncompressibleNavierStokesStepper(Stepper):
         self._plan = None  # (key, domain struct, bc table tensor, n_bc)
         # BC cell list (XlbCollisionParams.bc_cells): (key, sorted cell indices on the device, per-plane offsets on the host)
         self._cells = None
-        self._use_cell_list = bool(self.backend_config.get("bc_cell_list", True)) if self.backend_config else True
+        # backend_config["bc_cell_list"]: True / False force it; "auto" (default) uses it when the block holds enough such
+        # cells for the second launch to pay for itself (B200: ~1e5 cells; below that the in-kernel path is ahead,
+        # profiles/r1q_*: 384x128x128 sphere 22.4k -> 21.6k MLUPS with the list, 192x1536x1536 wind tunnel 21.5k -> 23.9k)
+        self._use_cell_list = self.backend_config.get("bc_cell_list", "auto") if self.backend_config else "auto"
 
     # ------------------------------------------------------------------ setup (nse_stepper.py:99-205)
     def prepare_fields(self, initializer=None):
@@ -115,6 +118,26 @@ class IncompressibleNavierStokesStepper(Stepper):
                 start = (self.grid.x_offset - self.grid.halo,) + (0,) * (self.velocity_set.d - 1)
                 gshape = self.grid.global_shape
             bc_mask, missing_mask = masker(with_indices, bc_mask, missing_mask, start, gshape)
+        # mesh-based boundary conditions (nse_stepper.py:165-203): voxelised on the device, after the index-based ones
+        with_vertices = [bc for bc in boundary_conditions if getattr(bc, "mesh_vertices", None) is not None]
+        if with_vertices:
+            if self.velocity_set.d != 3:
+                raise NotImplementedError("mesh-based boundary conditions need a 3-D velocity set (mesh_boundary_masker.py:36-39)")
+            from ..boundary_masker import MeshMaskerRay, MeshVoxelizationMethod
+
+            start = None
+            gshape = None
+            if getattr(self.grid, "halo", 0) or getattr(self.grid, "x_offset", 0):
+                start = (self.grid.x_offset - self.grid.halo, 0, 0)
+                gshape = self.grid.global_shape
+            for bc in with_vertices:
+                method = bc.voxelization_method if bc.voxelization_method is not None else MeshVoxelizationMethod("RAY")
+                if method.id != MeshVoxelizationMethod("RAY").id:
+                    raise NotImplementedError(f"voxelization method {method.name}: the CUDA backend implements RAY (ray.py) only")
+                if bc.needs_mesh_distance:
+                    raise NotImplementedError("boundary conditions that need the mesh distance (HybridBC) are outside the CUDA backend's scope")
+                mesh_masker = MeshMaskerRay(velocity_set=self.velocity_set, precision_policy=self.precision_policy, compute_backend=self.compute_backend)
+                _, bc_mask, missing_mask = mesh_masker(bc, None, bc_mask, missing_mask, start, gshape)
         return bc_mask, missing_mask
 
     # ------------------------------------------------------------------ BC table
@@ -143,6 +166,8 @@ class IncompressibleNavierStokesStepper(Stepper):
     _LISTED_KINDS = (_lib.BC_DONOTHING, _lib.BC_ZOUHE_VELOCITY, _lib.BC_ZOUHE_PRESSURE, _lib.BC_EXTRAPOLATION,
                      _lib.BC_REGULARIZED_VELOCITY, _lib.BC_REGULARIZED_PRESSURE)
 
+    CELL_LIST_MIN = 100_000
+
     def _bc_cell_list(self, f_0, bc_mask):
         """Sorted device list of the cells whose BC kind needs the per-cell engine (Zou-He, regularized, extrapolation
         outflow, do-nothing) plus its per-plane offsets, cached per ``bc_mask`` content.  ``xlb_step_ex`` then updates
@@ -160,7 +185,7 @@ class IncompressibleNavierStokesStepper(Stepper):
         args = (byref(dom), bc_mask.data_ptr(), table.data_ptr(), 0, 0, int(dom.nx))
         check(lib().xlb_list_bc_cells(*args, None, 0, count.data_ptr(), stream_ptr()), "IncompressibleNavierStokesStepper")
         n = int(count.item())
-        if n == 0:
+        if n == 0 or (self._use_cell_list == "auto" and n < self.CELL_LIST_MIN):
             return self._cells
         cells = torch.empty(n, dtype=torch.int64, device=bc_mask.device)
         count.zero_()
