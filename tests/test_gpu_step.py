@@ -223,6 +223,13 @@ BULK_CASES = [
     cases.periodic((3, 3, 256), lattice="D3Q27", collision="KBC"),
     cases.cavity2d(0, shape=(20, 256), collision="KBC"),
     cases.sphere3d((28, 16, 128)),  # D3Q27 KBC on a 128-wide grid: NT = 64 tiles
+    # FP16 storage: packed-half2 consumer of the staged rows (512-cell tiles where nz allows, else 256)
+    cases.cavity3d(0, shape=(4, 5, 512), omega=1.7, policy="FP32FP16"),
+    cases.cavity3d(0, shape=(3, 4, 1024), omega=1.2, policy="FP32FP16"),
+    cases.periodic((3, 3, 512), policy="FP32FP16"),
+    cases.sphere3d((28, 16, 256), policy="FP32FP16"),
+    cases.sphere3d((24, 16, 512), policy="FP32FP16", lattice="D3Q19", collision="BGK", inlet="pressure"),
+    cases.cavity3d(0, shape=(4, 4, 768), omega=1.9, policy="FP32FP16"),
 ]
 
 

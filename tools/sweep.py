@@ -33,12 +33,12 @@ def build(instance, variants):
         print("built", path)
 
 
-def run(workload, steps, only="", variant=0):
+def run(workload, steps, only="", variant=0, shape=None):
     rows = []
     for lib in sorted(glob.glob(os.path.join(SWEEP_DIR, f"lib_{only}*.so"))):
         env = dict(os.environ, XLB_B200_LIB=lib, XLB_B200_TUNING_LIB="1")
         r = subprocess.run(
-            [sys.executable, os.path.join(ROOT, "bench.py"), "--workload", workload, "--steps", str(steps), "--warmup", "3", "--no-e2e", "--no-cpu-baseline", "--variant", str(variant)],
+            [sys.executable, os.path.join(ROOT, "bench.py"), "--workload", workload, "--steps", str(steps), "--warmup", "3", "--no-e2e", "--no-cpu-baseline", "--variant", str(variant)] + (["--shape", shape] if shape else []),
             env=env, capture_output=True, text=True,
         )
         line = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
@@ -61,4 +61,5 @@ if __name__ == "__main__":
             steps = int(sys.argv[sys.argv.index("--steps") + 1])
         only = sys.argv[sys.argv.index("--only") + 1] if "--only" in sys.argv else ""
         variant = int(sys.argv[sys.argv.index("--variant") + 1]) if "--variant" in sys.argv else 0
-        run(sys.argv[2], steps, only, variant)
+        shape = sys.argv[sys.argv.index("--shape") + 1] if "--shape" in sys.argv else None
+        run(sys.argv[2], steps, only, variant, shape)

@@ -14,6 +14,7 @@
 // Requirements (checked on the host, otherwise the vector kernel runs): nz % TZ == 0, 16-byte aligned rows.
 #pragma once
 #include "xlb_step.cuh"
+#include "xlb_step_h2.cuh"
 
 namespace xlb {
 
@@ -67,8 +68,11 @@ struct BulkLayout {
     static size_t smem_bytes(int stages) { return (size_t)stages * STAGE_BYTES + 128; }
 };
 
-template <typename T, typename S, int Q, int COLL, int C, int NT, int STAGES, int MINB, bool HAS_BC, bool HALF = false>
+// H2 (FP16 storage only): the staged rows are read as packed half2 words -- thread t owns the cell pairs
+// (2t, 2t+1) + k*2*NT of the tile -- and stay packed in registers (PackedH2, see xlb_step_h2.cuh) through the collision.
+template <typename T, typename S, int Q, int COLL, int C, int NT, int STAGES, int MINB, bool HAS_BC, bool HALF = false, bool H2 = false>
 __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_constant__ StepParams p) {
+    static_assert(!H2 || (std::is_same<S, __half>::value && std::is_same<T, float>::value && C % 2 == 0), "H2: FP32 compute, FP16 storage, even C");
     constexpr int TZ = NT * C;
     using L = BulkLayout<S, Q, TZ, HAS_BC>;
     constexpr int HE = L::HE;
@@ -156,6 +160,125 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
         const unsigned char* stage = smem_raw + (size_t)s * L::STAGE_BYTES;
         const S* pops = reinterpret_cast<const S*>(stage);
         mbar_wait(&full[s], parity);
+        if constexpr (H2) {
+            // ---- staged rows -> packed registers.  Pair k of thread t = cells z0 + 2t + k*2NT (+1); a pull shift of +-1
+            // straddles two 32-bit words of the staged row: two conflict-free LDS.32 and one byte permute.
+            constexpr int W = C / 2;
+            PackedH2<Q, W> pk;
+            const uint32_t* words = reinterpret_cast<const uint32_t*>(stage);
+            static_for<Q>([&](auto lc) {
+                XLB_IDX(l, lc);
+                constexpr int cz = Dir<Q, l>::cz;
+                constexpr int base = (l * L::ROW + HE) / 2;  // word index of cell 0 of the tile in row l (ROW and HE are even)
+#pragma unroll
+                for (int k = 0; k < W; ++k) {
+                    const int w = base + tid + k * NT;
+                    if (cz == 0) pk.w[l][k] = words[w];
+                    else if (cz == 1) pk.w[l][k] = __byte_perm(words[w - 1], words[w], 0x5432);  // elements 2t-1, 2t
+                    else pk.w[l][k] = __byte_perm(words[w], words[w + 1], 0x5432);                  // elements 2t+1, 2t+2
+                }
+            });
+            uint32_t idp[W];  // the two bc ids of each pair
+            bool any_bc = false;
+#pragma unroll
+            for (int k = 0; k < W; ++k) {
+                idp[k] = HAS_BC ? *reinterpret_cast<const unsigned short*>(stage + L::POP_BYTES + 2 * (tid + k * NT)) : 0u;
+                any_bc |= idp[k] != 0;
+            }
+            __syncwarp();
+            unsigned prev = 0;
+            if (lane == 0) prev = stage_arrive(&arrived[s]);
+            prev = __shfl_sync(0xffffffffu, prev, 0);
+            if ((prev + 1) % NW == 0 && (long long)t + (long long)STAGES * gridDim.x < total) issue(t + STAGES * (int)gridDim.x, s);
+
+            static_for<W>([&](auto kc) {
+                XLB_IDX(k, kc);
+                const int zc = z0 + 2 * (tid + k * NT);
+                const long long cell0 = x * plane + (long long)y * p.nz + zc;
+                bool fw[2] = {false, false}, eq[2] = {false, false}, hf[2] = {false, false};
+                bool slow = false;
+                int id2[2] = {(int)(idp[k] & 0xffu), (int)(idp[k] >> 8)};
+                if (HAS_BC && idp[k] != 0) {
+#pragma unroll
+                    for (int j = 0; j < 2; ++j) {
+                        if (id2[j]) {
+                            const int kind = p.bct[id2[j]].kind;
+                            fw[j] = kind == XLB_BC_FULLWAY;
+                            eq[j] = kind == XLB_BC_EQUILIBRIUM;
+                            const bool here = p.cells == nullptr || !bc_is_listed(kind);
+                            if constexpr (HALF) {
+                                hf[j] = kind == XLB_BC_HALFWAY;
+                                slow |= bc_is_complex(kind) && !hf[j] && here;
+                            } else {
+                                slow |= bc_is_complex(kind) && here;
+                            }
+                        }
+                    }
+                }
+                if (HAS_BC && slow) {
+                    cell_update_generic<T, S, Q, COLL>(p, x, y, zc);
+                    cell_update_generic<T, S, Q, COLL>(p, x, y, zc + 1);
+                } else {
+                    constexpr bool FORCED = (COLL & XLB_COLL_FORCED) != 0;
+                    const bool pair_full = HAS_BC && (fw[0] || fw[1]);
+                    if (FORCED || !XLB_PACKED(COLL) || (HAS_BC && (eq[0] || eq[1] || hf[0] || hf[1]))) {
+                        T g[Q][2];
+#pragma unroll
+                        for (int l = 0; l < Q; ++l) {
+                            const float2 v2 = h2_to_f2(pk.w[l][k]);
+                            g[l][0] = v2.x;
+                            g[l][1] = v2.y;
+                        }
+                        if constexpr (HAS_BC && HALF) {
+                            if (hf[0] || hf[1]) {  // HalfwayBounceBackBC, STREAMING step (bc_halfway_bounce_back.py:116-134)
+                                uint32_t mb[2] = {0, 0};
+                                static_for<Q>([&](auto lc) {
+                                    XLB_IDX(l, lc);
+                                    const Vec<uint8_t, 2> m = ld_vec<uint8_t, 2>(p.missing + l * p.mqs + cell0);
+                                    mb[0] |= (m.v[0] ? 1u : 0u) << l;
+                                    mb[1] |= (m.v[1] ? 1u : 0u) << l;
+                                });
+                                if (!hf[0]) mb[0] = 0;
+                                if (!hf[1]) mb[1] = 0;
+                                const double* tab0 = p.bct[id2[0]].table;
+                                const double* tab1 = p.bct[id2[1]].table;
+                                static_for<Q>([&](auto lc) {
+                                    XLB_IDX(l, lc);
+                                    const float2 pre = h2_to_f2(*reinterpret_cast<const uint32_t*>(f0 + Dir<Q, l>::o * p.qs + cell0));
+                                    if (mb[0] & (1u << l)) g[l][0] = pre.x + static_cast<T>(tab0[l]);
+                                    if (mb[1] & (1u << l)) g[l][1] = pre.y + static_cast<T>(tab1[l]);
+                                });
+                            }
+                        }
+#pragma unroll
+                        for (int j = 0; j < 2; ++j) {
+                            if (HAS_BC && eq[j]) {  // EquilibriumBC (STREAMING step)
+                                const double* tab = p.bct[id2[j]].table;
+#pragma unroll
+                                for (int l = 0; l < Q; ++l) g[l][j] = static_cast<T>(tab[l]);
+                            }
+                        }
+                        if constexpr (XLB_PACKED(COLL)) {
+                            collide_cols<F2, T, Q, COLL, 2, 0>(g, ca, fw, pair_full);
+                        } else {
+                            collide_cols<T, T, Q, COLL, 2, 0>(g, ca, &fw[0], fw[0]);
+                            collide_cols<T, T, Q, COLL, 2, 1>(g, ca, &fw[1], fw[1]);
+                        }
+#pragma unroll
+                        for (int l = 0; l < Q; ++l) pk.w[l][k] = f2_to_h2(g[l][0], g[l][1]);
+                    } else {
+                        collide_cols<F2, T, Q, COLL, C, 2 * k>(pk, ca, fw, pair_full);
+                    }
+                    uint32_t* ql = reinterpret_cast<uint32_t*>(f1 + cell0);
+#pragma unroll
+                    for (int l = 0; l < Q; ++l) {
+                        *ql = pk.w[l][k];
+                        ql += p.qs / 2;
+                    }
+                }
+            });
+            continue;
+        }
         // ---- staged rows -> registers (pull shift = index offset)
         T f[Q][C];
         static_for<Q>([&](auto lc) {

@@ -12,6 +12,12 @@
 #pragma once
 #include "xlb_step.cuh"
 
+// 1: always widen a pair to FP32 registers before the collision (one convert per element instead of one per read);
+// tuning knob, needs the register budget of V = 8 at 3 blocks per SM
+#ifndef XLB_TUNE_H2_WIDEN
+#define XLB_TUNE_H2_WIDEN 0
+#endif
+
 namespace xlb {
 
 XLB_D uint32_t ld_if_u16(const void* ptr, bool pred, uint32_t keep) {
@@ -179,7 +185,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_h2_kernel(const __gri
             fw[0] = (m_full >> (2 * jp)) & 1u;
             fw[1] = (m_full >> (2 * jp + 1)) & 1u;
         }
-        if (FORCED || !XLB_PACKED(COLL) || pair_bc) {
+        if (FORCED || !XLB_PACKED(COLL) || pair_bc || XLB_TUNE_H2_WIDEN) {
             T g[Q][2];
 #pragma unroll
             for (int l = 0; l < Q; ++l) {

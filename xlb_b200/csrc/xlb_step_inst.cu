@@ -19,10 +19,12 @@
 #define XLB_TUNE_BLOCK 128
 #endif
 // default (V, MINB) per instance from the B200 sweeps recorded in profiles/ (tools/sweep.py)
-template <typename S, int Q>
-constexpr int default_vec() { return sizeof(S) == 8 ? 2 : (Q == 27 ? 2 : 4); }
-template <typename S, int Q>
-constexpr int default_minb() { return sizeof(S) == 8 ? 4 : (Q == 27 ? 4 : (sizeof(S) == 2 ? 5 : 4)); }
+// FP16 storage (packed-half2 kernel): 8 cells per thread = one 128-bit load per population at 12 warps per SM
+// (profiles/sweep9_f16_h2.log, sweep10_f16_h2_v8.log); rows that are only a multiple of 4 cells wide run V = 4.
+template <typename T, typename S, int Q>
+constexpr int default_vec() { return sizeof(S) == 8 ? 2 : (Q == 27 ? 2 : ((sizeof(S) == 2 && sizeof(T) == 4 && XLB_TUNE_H2) ? 8 : 4)); }
+template <typename S, int Q, int V>
+constexpr int default_minb() { return sizeof(S) == 8 ? 4 : (Q == 27 ? 4 : (sizeof(S) == 2 ? (V == 8 ? 3 : 5) : 4)); }
 
 namespace xlb {
 
@@ -39,7 +41,7 @@ static int launch_vector(const StepParams& p0, cudaStream_t st) {
 #ifdef XLB_TUNE_MINB
     constexpr int MINB = XLB_TUNE_MINB;
 #else
-    constexpr int MINB = (V == 1) ? 4 : default_minb<S, Q>();
+    constexpr int MINB = (V == 1) ? 4 : default_minb<S, Q, V>();
 #endif
     if constexpr (XLB_TUNE_H2 && std::is_same<S, __half>::value && std::is_same<T, float>::value && V >= 2) {
         step_vector_h2_kernel<Q, COLL, V, BLOCK, MINB, HAS_BC, HALF><<<grid, BLOCK, 0, st>>>(p);
@@ -60,13 +62,25 @@ static int launch_vector(const StepParams& p0, cudaStream_t st) {
 #endif
 
 // persistent bulk-copy-staged kernel (xlb_step_bulk.cuh); returns -1000 when the shape does not qualify
-template <typename T, typename S, int Q, int COLL, int C, int NT, bool HAS_BC, bool HALF = false>
+// FP16 storage: packed-half2 consumer of the staged rows (H2), tile of C = 4 cells per thread (1 KB rows) where nz allows
+#ifndef XLB_TUNE_HC
+#define XLB_TUNE_HC 4
+#endif
+#ifndef XLB_TUNE_HSTAGES
+#define XLB_TUNE_HSTAGES 3
+#endif
+#ifndef XLB_TUNE_HBMINB
+#define XLB_TUNE_HBMINB 4
+#endif
+
+template <typename T, typename S, int Q, int COLL, int C, int NT, bool HAS_BC, bool HALF = false, bool H2 = false>
 static int launch_bulk(const StepParams& p, cudaStream_t st) {
     constexpr int TZ = NT * C;
-    constexpr int STAGES = XLB_TUNE_STAGES;
+    constexpr int STAGES = H2 ? XLB_TUNE_HSTAGES : XLB_TUNE_STAGES;
     using L = BulkLayout<S, Q, TZ, HAS_BC>;
-    constexpr int BMINB = (XLB_TUNE_BMINB * 128 / NT) > 0 ? (XLB_TUNE_BMINB * 128 / NT) : 1;  // same register budget per thread for every NT
-    auto kern = step_bulk_kernel<T, S, Q, COLL, C, NT, STAGES, BMINB, HAS_BC, HALF>;
+    constexpr int BM0 = H2 ? XLB_TUNE_HBMINB : XLB_TUNE_BMINB;
+    constexpr int BMINB = (BM0 * 128 / NT) > 0 ? (BM0 * 128 / NT) : 1;  // same register budget per thread for every NT
+    auto kern = step_bulk_kernel<T, S, Q, COLL, C, NT, STAGES, BMINB, HAS_BC, HALF, H2>;
     static int blocks_per_sm = 0, n_sm = 0;
     const size_t smem = L::smem_bytes(STAGES);
     if (blocks_per_sm == 0) {
@@ -93,6 +107,11 @@ static int try_bulk(const StepParams& p, cudaStream_t st) {
     const uintptr_t a0 = reinterpret_cast<uintptr_t>(p.f0), am = reinterpret_cast<uintptr_t>(p.bc_mask);
     const bool aligned = (a0 % 16 == 0) && ((p.qs * sizeof(S)) % 16 == 0) && ((p.nz * sizeof(S)) % 16 == 0) && (!HAS_BC || am % 16 == 0);
     if (!aligned) return -1000;
+    if constexpr (XLB_TUNE_H2 && std::is_same<S, __half>::value && std::is_same<T, float>::value) {
+        if (p.nz % (128 * XLB_TUNE_HC) == 0) return launch_bulk<T, S, Q, COLL, XLB_TUNE_HC, 128, HAS_BC, HALF, true>(p, st);
+        if (XLB_TUNE_HC != 2 && p.nz % 256 == 0) return launch_bulk<T, S, Q, COLL, 2, 128, HAS_BC, HALF, true>(p, st);
+        return -1000;
+    }
 #ifdef XLB_TUNE_NT
     if (p.nz % (XLB_TUNE_NT * C) == 0) return launch_bulk<T, S, Q, COLL, C, XLB_TUNE_NT, HAS_BC, HALF>(p, st);
 #else
@@ -132,7 +151,7 @@ static int step_main(const StepParams& p, int variant, cudaStream_t st) {
 #ifdef XLB_TUNE_V
     constexpr int VMAX = XLB_TUNE_V;
 #else
-    constexpr int VMAX = default_vec<S, Q>();
+    constexpr int VMAX = default_vec<T, S, Q>();
 #endif
     const bool has_bc = p.bc_mask != nullptr && p.bct != nullptr;
     // half-way obstacles get the instance with the vectorised half-way path (unknown kind mask: assume present)
@@ -158,7 +177,7 @@ static int step_main(const StepParams& p, int variant, cudaStream_t st) {
     const uintptr_t a0 = reinterpret_cast<uintptr_t>(p.f0), a1 = reinterpret_cast<uintptr_t>(p.f1);
     const bool vec_ok = (p.nz % VMAX == 0) && (p.qs % VMAX == 0) && (a0 % (VMAX * sizeof(S)) == 0) && (a1 % (VMAX * sizeof(S)) == 0) &&
                         (!has_bc || reinterpret_cast<uintptr_t>(p.bc_mask) % VMAX == 0);
-    if (variant == XLB_VARIANT_VECTOR && !vec_ok) return set_error(XLB_EALIGN, "xlb_step: vector variant needs nz, q_stride and base pointers aligned to the vector width");
+    if (variant == XLB_VARIANT_VECTOR && !vec_ok && !(VMAX == 8 && p.nz % 4 == 0)) return set_error(XLB_EALIGN, "xlb_step: vector variant needs nz, q_stride and base pointers aligned to the vector width");
     // AUTO: the bulk-staged pipeline where the B200 sweeps show it ahead of the vector kernel (D3Q27 KBC, compute-heavy)
     if constexpr (Q == 27 && COLL == XLB_KBC && sizeof(S) == 4) {
         // ... except on blocks where a large half-way obstacle covers more than ~1 % of the cells: the direct loads of its
@@ -171,6 +190,15 @@ static int step_main(const StepParams& p, int variant, cudaStream_t st) {
     if (vec_ok && variant != XLB_VARIANT_SCALAR) {
         if (!has_bc) return launch_vector<T, S, Q, COLL, VMAX, false>(p, st);
         return half ? launch_vector<T, S, Q, COLL, VMAX, true, true>(p, st) : launch_vector<T, S, Q, COLL, VMAX, true, false>(p, st);
+    }
+    if constexpr (VMAX == 8) {  // FP16 rows that are a multiple of 4 but not of 8 cells
+        constexpr int V4 = 4;
+        const bool v4_ok = (p.nz % V4 == 0) && (p.qs % V4 == 0) && (a0 % (V4 * sizeof(S)) == 0) && (a1 % (V4 * sizeof(S)) == 0) &&
+                           (!has_bc || reinterpret_cast<uintptr_t>(p.bc_mask) % V4 == 0);
+        if (v4_ok && variant != XLB_VARIANT_SCALAR) {
+            if (!has_bc) return launch_vector<T, S, Q, COLL, V4, false>(p, st);
+            return half ? launch_vector<T, S, Q, COLL, V4, true, true>(p, st) : launch_vector<T, S, Q, COLL, V4, true, false>(p, st);
+        }
     }
     return has_bc ? launch_vector<T, S, Q, COLL, 1, true>(p, st) : launch_vector<T, S, Q, COLL, 1, false>(p, st);
 }
