@@ -13,9 +13,9 @@
 #include "xlb_step.cuh"
 
 // 1: always widen a pair to FP32 registers before the collision (one convert per element instead of one per read);
-// tuning knob, needs the register budget of V = 8 at 3 blocks per SM
+// needs the register budget the V = 8 instance runs with (168-204 registers per thread), +2 % there
 #ifndef XLB_TUNE_H2_WIDEN
-#define XLB_TUNE_H2_WIDEN 0
+#define XLB_TUNE_H2_WIDEN -1  // -1: widen where the register budget allows it (V = 8), profiles/sweep11_f16_*.log
 #endif
 
 namespace xlb {
@@ -185,7 +185,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_h2_kernel(const __gri
             fw[0] = (m_full >> (2 * jp)) & 1u;
             fw[1] = (m_full >> (2 * jp + 1)) & 1u;
         }
-        if (FORCED || !XLB_PACKED(COLL) || pair_bc || XLB_TUNE_H2_WIDEN) {
+        constexpr bool WIDEN = XLB_TUNE_H2_WIDEN < 0 ? (V == 8) : (XLB_TUNE_H2_WIDEN != 0);
+        if (FORCED || !XLB_PACKED(COLL) || pair_bc || WIDEN) {
             T g[Q][2];
 #pragma unroll
             for (int l = 0; l < Q; ++l) {

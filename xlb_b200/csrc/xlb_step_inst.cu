@@ -17,6 +17,8 @@
 #endif
 #ifndef XLB_TUNE_BLOCK
 #define XLB_TUNE_BLOCK 128
+#else
+#define XLB_TUNE_BLOCK_SET 1
 #endif
 // default (V, MINB) per instance from the B200 sweeps recorded in profiles/ (tools/sweep.py)
 // FP16 storage (packed-half2 kernel): 8 cells per thread = one 128-bit load per population at 12 warps per SM
@@ -24,13 +26,18 @@
 template <typename T, typename S, int Q>
 constexpr int default_vec() { return sizeof(S) == 8 ? 2 : (Q == 27 ? 2 : ((sizeof(S) == 2 && sizeof(T) == 4 && XLB_TUNE_H2) ? 8 : 4)); }
 template <typename S, int Q, int V>
-constexpr int default_minb() { return sizeof(S) == 8 ? 4 : (Q == 27 ? 4 : (sizeof(S) == 2 ? (V == 8 ? 3 : 5) : 4)); }
+constexpr int default_minb() { return sizeof(S) == 8 ? 4 : (Q == 27 ? 4 : (sizeof(S) == 2 ? 5 : 4)); }  // FP16: 5 blocks of 64 (V = 8) or of 128 (V = 4)
 
 namespace xlb {
 
 template <typename T, typename S, int Q, int COLL, int V, bool HAS_BC, bool HALF = false>
 static int launch_vector(const StepParams& p0, cudaStream_t st) {
+    constexpr bool USE_H2 = XLB_TUNE_H2 && std::is_same<S, __half>::value && std::is_same<T, float>::value && V >= 2;
+#ifdef XLB_TUNE_BLOCK_SET
     constexpr int BLOCK = XLB_TUNE_BLOCK;
+#else
+    constexpr int BLOCK = (USE_H2 && V == 8) ? 64 : XLB_TUNE_BLOCK;  // finer block granularity at 168-204 registers per thread
+#endif
     StepParams p = p0;
     p.ntz = p.nz / V;
     p.ntz_shift = -1;
@@ -43,7 +50,7 @@ static int launch_vector(const StepParams& p0, cudaStream_t st) {
 #else
     constexpr int MINB = (V == 1) ? 4 : default_minb<S, Q, V>();
 #endif
-    if constexpr (XLB_TUNE_H2 && std::is_same<S, __half>::value && std::is_same<T, float>::value && V >= 2) {
+    if constexpr (USE_H2) {
         step_vector_h2_kernel<Q, COLL, V, BLOCK, MINB, HAS_BC, HALF><<<grid, BLOCK, 0, st>>>(p);
     } else {
         step_vector_kernel<T, S, Q, COLL, V, BLOCK, MINB, HAS_BC, HALF><<<grid, BLOCK, 0, st>>>(p);
@@ -70,7 +77,7 @@ static int launch_vector(const StepParams& p0, cudaStream_t st) {
 #define XLB_TUNE_HSTAGES 3
 #endif
 #ifndef XLB_TUNE_HBMINB
-#define XLB_TUNE_HBMINB 4
+#define XLB_TUNE_HBMINB 3
 #endif
 
 template <typename T, typename S, int Q, int COLL, int C, int NT, bool HAS_BC, bool HALF = false, bool H2 = false>
