@@ -43,7 +43,9 @@ def main():
             ref, ref_bc, ref_mm = f_0.clone(), bc_mask.clone(), missing.clone()
             # distributed run
             dec = SlabDecomposition()
-            st, _ = build_product(case, decomposition=dec)
+            # with the overlap schedule the slab stepper also runs the BC-cell-list path (forced: these blocks are far
+            # below the size where "auto" would pick it), so its per-plane slicing is covered by the bitwise comparison
+            st, _ = build_product(case, backend_config={"bc_cell_list": True} if overlap else None, decomposition=dec)
             dst = distribute(st, st.grid, st.velocity_set, overlap=overlap)
             g_0, g_1, g_bc, g_mm = dst.prepare_fields()
             x0, n = dec.local_range(case["shape"][0])
