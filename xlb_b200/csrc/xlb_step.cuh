@@ -35,11 +35,20 @@ XLB_D int wrapn(int v, int n) {  // periodic wrap of an index that is at most a 
 
 // ------------------------------------------------------------------ generic per-cell engine
 // Handles every BC kind; all reads come from f0, the only write is the cell's own f1 column.
+// (body; the fused kernels call it through the __noinline__ wrapper below so that their fast path keeps its registers,
+// the dense kernels -- step_cells_kernel, step_generic_kernel -- inline it, which turns every p.* into a constant-bank
+// operand instead of a generic load through the by-reference parameter block)
 template <typename T, typename S, int Q, int COLL>
-__device__ __noinline__ void cell_update_generic(const StepParams& p, int x, int y, int z) {
+XLB_D void cell_update_generic_impl(const StepParams& p, int x, int y, int z) {
     const S* __restrict__ f0 = static_cast<const S*>(p.f0);
     S* __restrict__ f1 = static_cast<S*>(p.f1);
-    const long long cell = ((long long)x * p.ny + y) * p.nz + z;
+    const long long plane = (long long)p.ny * p.nz;
+    const long long cell = x * plane + (long long)y * p.nz + z;
+    // source offsets of the pull per axis, indexed by c (0 -> same, +1 -> minus side, -1 -> plus side): 6 wraps per cell
+    // instead of 3 per direction
+    const long long ox0 = x * plane, oxm = (p.x_periodic ? wrap1(x - 1, p.nx) : x - 1) * plane, oxp = (p.x_periodic ? wrap1(x + 1, p.nx) : x + 1) * plane;
+    const int oy0 = y * p.nz, oym = wrap1(y - 1, p.ny) * p.nz, oyp = wrap1(y + 1, p.ny) * p.nz;
+    const int oz0 = z, ozm = wrap1(z - 1, p.nz), ozp = wrap1(z + 1, p.nz);
     const int id = p.bc_mask ? p.bc_mask[cell] : 0;
     int kind = XLB_BC_NONE;
     const XlbBcEntry* e = nullptr;
@@ -52,11 +61,10 @@ __device__ __noinline__ void cell_update_generic(const StepParams& p, int x, int
     static_for<Q>([&](auto lc) {
         XLB_IDX(l, lc);
         using D = Dir<Q, l>;
-        int xs = x - D::cx;
-        if (p.x_periodic) xs = wrap1(xs, p.nx);
-        const int ys = wrap1(y - D::cy, p.ny);
-        const int zs = wrap1(z - D::cz, p.nz);
-        f[l][0] = to_compute<T, S>(f0[l * p.qs + ((long long)xs * p.ny + ys) * p.nz + zs]);
+        const long long ox = D::cx == 0 ? ox0 : (D::cx == 1 ? oxm : oxp);
+        const int oy = D::cy == 0 ? oy0 : (D::cy == 1 ? oym : oyp);
+        const int oz = D::cz == 0 ? oz0 : (D::cz == 1 ? ozm : ozp);
+        f[l][0] = to_compute<T, S>(f0[l * p.qs + (ox + (oy + oz))]);
     });
     uint32_t miss = 0;
     if (kind >= XLB_BC_HALFWAY && kind != XLB_BC_DONOTHING) {
@@ -94,21 +102,30 @@ __device__ __noinline__ void cell_update_generic(const StepParams& p, int x, int
     if (kind == XLB_BC_EXTRAPOLATION) {
         const T cs = T(1.0) / sqrt(T(3.0));
         const int xn = x - e->normal[0], yn = y - e->normal[1], zn = z - e->normal[2];
+        // per-axis source offsets of the pull at the interior neighbour x - n (same indexing by c as above)
+        const long long nx0 = (p.x_periodic ? wrapn(xn, p.nx) : xn) * plane, nxm = (p.x_periodic ? wrapn(xn - 1, p.nx) : xn - 1) * plane,
+                        nxp = (p.x_periodic ? wrapn(xn + 1, p.nx) : xn + 1) * plane;
+        const int ny0 = wrapn(yn, p.ny) * p.nz, nym = wrapn(yn - 1, p.ny) * p.nz, nyp = wrapn(yn + 1, p.ny) * p.nz;
+        const int nz0 = wrapn(zn, p.nz), nzm = wrapn(zn - 1, p.nz), nzp = wrapn(zn + 1, p.nz);
         static_for<Q>([&](auto lc) {
             XLB_IDX(l, lc);
             using D = Dir<Q, l>;
             if (miss & (1u << l)) {
-                int xs = xn - D::cx;
-                if (p.x_periodic) xs = wrapn(xs, p.nx);
-                const int ys = wrapn(yn - D::cy, p.ny);
-                const int zs = wrapn(zn - D::cz, p.nz);
-                const T nb = to_compute<T, S>(f0[l * p.qs + ((long long)xs * p.ny + ys) * p.nz + zs]);
+                const long long ox = D::cx == 0 ? nx0 : (D::cx == 1 ? nxm : nxp);
+                const int oy = D::cy == 0 ? ny0 : (D::cy == 1 ? nym : nyp);
+                const int oz = D::cz == 0 ? nz0 : (D::cz == 1 ? nzm : nzp);
+                const T nb = to_compute<T, S>(f0[l * p.qs + (ox + (oy + oz))]);
                 f[D::o][0] = cs * nb + (T(1.0) - cs) * fps[l];
             }
         });
     }
 #pragma unroll
     for (int l = 0; l < Q; ++l) f1[l * p.qs + cell] = to_store<S, T>(f[l][0]);
+}
+
+template <typename T, typename S, int Q, int COLL>
+__device__ __noinline__ void cell_update_generic(const StepParams& p, int x, int y, int z) {
+    cell_update_generic_impl<T, S, Q, COLL>(p, x, y, z);
 }
 
 // every cell through the generic engine (variant XLB_VARIANT_GENERIC; cross-check + odd shapes)
@@ -118,7 +135,7 @@ __global__ void __launch_bounds__(128) step_generic_kernel(const __grid_constant
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= row) return;
     const int x = p.x_begin + blockIdx.y;
-    cell_update_generic<T, S, Q, COLL>(p, x, (int)(i / p.nz), (int)(i % p.nz));
+    cell_update_generic_impl<T, S, Q, COLL>(p, x, (int)(i / p.nz), (int)(i % p.nz));
 }
 
 // the cells of the BC cell list (XlbCollisionParams.bc_cells) through the generic engine: consecutive threads take
@@ -131,11 +148,17 @@ __global__ void __launch_bounds__(128) step_cells_kernel(const __grid_constant__
     if (i >= p.n_cells) return;
     const long long cell = p.cells[i];
     const long long plane = (long long)p.ny * p.nz;
-    const int x = (int)(cell / plane);
-    const int r = (int)(cell - x * plane);
+    int x, r;
+    if (cell < (1ll << 31) && plane < (1ll << 31)) {  // 32-bit division where the block allows it
+        x = (int)((unsigned)cell / (unsigned)plane);
+        r = (int)((unsigned)cell - (unsigned)x * (unsigned)plane);
+    } else {
+        x = (int)(cell / plane);
+        r = (int)(cell - x * plane);
+    }
     const int y = r / p.nz;
     if (x < p.x_begin || x >= p.x_end) return;
-    cell_update_generic<T, S, Q, COLL>(p, x, y, r - y * p.nz);
+    cell_update_generic_impl<T, S, Q, COLL>(p, x, y, r - y * p.nz);
 }
 
 // ------------------------------------------------------------------ fused vector kernel (K1)
