@@ -14,6 +14,12 @@
 
 // 1: always widen a pair to FP32 registers before the collision (one convert per element instead of one per read);
 // needs the register budget the V = 8 instance runs with (168-204 registers per thread), +2 % there
+// 1: BC-free groups of four cells collide as one F4 number (xlb_math.cuh: two independent packed streams, twice the ILP
+// per warp) on the packed storage.  Measured SLOWER on B200 (57.6 k vs 68.3 k MLUPS, profiles/sweep12_f16_quad_f4.log): the
+// doubled temporaries cost more than the extra ILP gains, so the kernel is not limited by per-warp dependency chains.
+#ifndef XLB_TUNE_H2_QUAD
+#define XLB_TUNE_H2_QUAD 0
+#endif
 #ifndef XLB_TUNE_H2_WIDEN
 #define XLB_TUNE_H2_WIDEN -1  // -1: widen where the register budget allows it (V = 8), profiles/sweep11_f16_*.log
 #endif
@@ -174,9 +180,11 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_h2_kernel(const __gri
     // ---- one pair of cells at a time.  Pairs without streaming-step BC cells collide straight on the packed storage
     // (widened on access, narrowed once on the final set); pairs that hold an EquilibriumBC / half-way cell, and the
     // forced collisions (which read their own output), are widened to FP32 first so that every intermediate stays FP32.
-    static_for<W>([&](auto jc) {
+    constexpr bool FORCED = (COLL & XLB_COLL_FORCED) != 0;
+    // QUAD: BC-free groups of four cells collide as one F4 (two independent packed streams: twice the ILP per warp)
+    constexpr bool QUAD = XLB_TUNE_H2_QUAD && (V % 4 == 0) && !FORCED && XLB_PACKED(COLL);
+    auto do_pair = [&](auto jc, bool force_widen) {
         XLB_IDX(jp, jc);
-        constexpr bool FORCED = (COLL & XLB_COLL_FORCED) != 0;
         constexpr uint32_t PAIR = 3u << (2 * jp);
         const bool pair_bc = HAS_BC && (((m_eq | m_half) & PAIR) != 0);
         const bool pair_full = HAS_BC && ((m_full & PAIR) != 0);
@@ -185,8 +193,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_h2_kernel(const __gri
             fw[0] = (m_full >> (2 * jp)) & 1u;
             fw[1] = (m_full >> (2 * jp + 1)) & 1u;
         }
-        constexpr bool WIDEN = XLB_TUNE_H2_WIDEN < 0 ? (V == 8) : (XLB_TUNE_H2_WIDEN != 0);
-        if (FORCED || !XLB_PACKED(COLL) || pair_bc || WIDEN) {
+        constexpr bool WIDEN = XLB_TUNE_H2_WIDEN < 0 ? (V == 8 && !QUAD) : (XLB_TUNE_H2_WIDEN != 0);
+        if (FORCED || !XLB_PACKED(COLL) || pair_bc || WIDEN || force_widen) {
             T g[Q][2];
 #pragma unroll
             for (int l = 0; l < Q; ++l) {
@@ -237,7 +245,27 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_h2_kernel(const __gri
         } else {
             collide_cols<F2, T, Q, COLL, V, 2 * jp>(pk, ca, fw, pair_full);
         }
-    });
+    };
+    if constexpr (QUAD) {
+        static_for<V / 4>([&](auto qc) {
+            XLB_IDX(jq, qc);
+            constexpr uint32_t QUADM = 15u << (4 * jq);
+            if (HAS_BC && ((m_eq | m_half) & QUADM) != 0) {  // a streaming-step BC cell in the group: pair by pair
+                do_pair(std::integral_constant<int, 2 * jq>{}, false);
+                do_pair(std::integral_constant<int, 2 * jq + 1>{}, false);
+            } else {
+                const bool quad_full = HAS_BC && ((m_full & QUADM) != 0);
+                bool fw4[4] = {false, false, false, false};
+                if (quad_full) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) fw4[k] = (m_full >> (4 * jq + k)) & 1u;
+                }
+                collide_cols<F4, T, Q, COLL, V, 4 * jq>(pk, ca, fw4, quad_full);
+            }
+        });
+    } else {
+        static_for<W>([&](auto jc) { do_pair(jc, false); });
+    }
     // ---- one aligned vector store per population
     S* ql = f1 + cell;
 #pragma unroll
