@@ -203,3 +203,63 @@ def test_stepper_with_mesh_obstacle_runs_and_matches_generic():
         rho = f_0.sum(dim=0)
         assert torch.isfinite(f_0).all() and rho.min() > 0.8 and rho.max() < 1.2
     assert torch.equal(outs[0], outs[1])
+
+
+# ----------------------------------------------------------------------------- host-side pieces (no GPU)
+def test_stl_roundtrip_and_grid_fit(tmp_path):
+    """read_stl returns what trimesh.load_mesh(..., process=False).vertices gives the reference's example
+    (windtunnel_3d.py:80-81): three consecutive vertex rows per facet, binary or ASCII."""
+    from xlb_b200.helper import ellipsoid_soup, fit_to_grid, read_stl, write_stl
+
+    v = ellipsoid_soup(radii=(2.0, 1.0, 0.5), centre=(1.0, -2.0, 3.0), subdivisions=2)
+    assert v.shape == (3 * 20 * 4**2, 3) and v.dtype == np.float32
+    # closed surface: every undirected edge is shared by exactly two triangles
+    tri = np.round(v.reshape(-1, 3, 3).astype(np.float64), 5)
+    edges = {}
+    for t in tri:
+        for a, b in ((0, 1), (1, 2), (2, 0)):
+            key = tuple(sorted((tuple(t[a]), tuple(t[b]))))
+            edges[key] = edges.get(key, 0) + 1
+    assert set(edges.values()) == {2}
+    p = str(tmp_path / "a.stl")
+    write_stl(p, v)
+    assert np.array_equal(read_stl(p), v)
+    q = str(tmp_path / "b.stl")
+    with open(q, "w") as fh:
+        fh.write("solid s\n")
+        for t in v.reshape(-1, 3, 3)[:5]:
+            fh.write("facet normal 0 0 0\n outer loop\n")
+            for a in t:
+                fh.write(f"  vertex {float(a[0])!r} {float(a[1])!r} {float(a[2])!r}\n")
+            fh.write(" endloop\nendfacet\n")
+        fh.write("endsolid s\n")
+    assert np.array_equal(read_stl(q), v[:15])
+    with open(str(tmp_path / "c.stl"), "w") as fh:
+        fh.write("not an stl\n")
+    with pytest.raises(ValueError):
+        read_stl(str(tmp_path / "c.stl"))
+    w, dx, area = fit_to_grid(v, (64, 32, 32))  # windtunnel_3d.py:83-100
+    ext = w.max(axis=0) - w.min(axis=0)
+    assert abs(ext.max() - 16.0) < 1e-4 and abs(w[:, 0].min() - 16.0) < 1e-4 and abs(w[:, 2].min() - 2.0) < 1e-4
+    assert abs((w[:, 1].min() + w[:, 1].max()) / 2 - 16.0) < 1e-4 and abs(area - ext[1] * ext[2]) < 1e-3 and dx > 0
+
+
+def test_mesh_bc_construction_and_method_registry():
+    """Mesh BCs keep their vertices until a masker consumes them; method ids are the reference's
+    (mesh_voxelization_method.py:12-17)."""
+    import xlb_b200 as xlb
+    from xlb_b200.compute_backend import ComputeBackend
+    from xlb_b200.operator.boundary_condition import HalfwayBounceBackBC
+    from xlb_b200.operator.boundary_masker import MeshVoxelizationMethod
+    from xlb_b200.precision_policy import PrecisionPolicy
+
+    pol = PrecisionPolicy.FP32FP32
+    vs = xlb.velocity_set.D3Q19(precision_policy=pol, compute_backend=ComputeBackend.CUDA)
+    xlb.init(velocity_set=vs, default_backend=ComputeBackend.CUDA, default_precision_policy=pol)
+    assert [MeshVoxelizationMethod(n).id for n in ("AABB", "RAY", "AABB_CLOSE", "WINDING")] == [1, 2, 3, 4]
+    assert MeshVoxelizationMethod("AABB_CLOSE", close_voxels=3).options == {"close_voxels": 3}
+    with pytest.raises(AssertionError):
+        MeshVoxelizationMethod("SDF")
+    verts = omm.box_mesh((2, 2, 2), (5, 5, 5))
+    bc = HalfwayBounceBackBC(mesh_vertices=verts, voxelization_method=MeshVoxelizationMethod("RAY"))
+    assert bc.indices is None and bc.mesh_vertices is verts and bc.voxelization_method.name == "RAY" and not bc.needs_mesh_distance

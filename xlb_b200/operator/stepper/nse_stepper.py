@@ -7,6 +7,8 @@ buffer swap left to the caller (examples/performance/mlups_3d.py:227-229).  One 
 ``xlb_step`` on the current torch CUDA stream; there is no host synchronisation inside.
 """
 
+import os
+
 import numpy as np
 import torch
 
@@ -67,6 +69,9 @@ class IncompressibleNavierStokesStepper(Stepper):
         # cells for the second launch to pay for itself (B200: ~1e5 cells; below that the in-kernel path is ahead,
         # profiles/r1q_*: 384x128x128 sphere 22.4k -> 21.6k MLUPS with the list, 192x1536x1536 wind tunnel 21.5k -> 23.9k)
         self._use_cell_list = self.backend_config.get("bc_cell_list", "auto") if self.backend_config else "auto"
+        env = os.environ.get("XLB_B200_BC_CELL_LIST")  # experiments: "1" / "0" override the default for steppers that do not set it
+        if env in ("0", "1") and not (self.backend_config and "bc_cell_list" in self.backend_config):
+            self._use_cell_list = env == "1"
 
     # ------------------------------------------------------------------ setup (nse_stepper.py:99-205)
     def prepare_fields(self, initializer=None):
