@@ -29,7 +29,6 @@ def build(instance, variants):
         name = instance + "__" + var.replace(",", "_").replace("=", "")
         path = os.path.join(SWEEP_DIR, f"lib_{name}.so")
         b.build(force=True, extra_flags=flags, lib_path=path, only={instance})
-        log = open(glob.glob(os.path.join(b.OBJ_DIR, f"step_{instance}_*.o.log"))[-1]).read() if False else ""
         print("built", path)
 
 
