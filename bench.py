@@ -319,6 +319,20 @@ def run_native(args):
         t += 1
     barrier()
 
+    # ---- optional: replay the step loop as CUDA graphs of --graph steps each (launch-bound small lattices)
+    graphed, graph_lps = None, None
+    if args.graph and world == 1:
+        from xlb_b200.operator.stepper import GraphedSteps
+
+        if args.steps % args.graph:
+            raise SystemExit("--steps must be a multiple of --graph")
+        c0 = _lib.launch_count()
+        graphed = GraphedSteps(stepper, f_0, f_1, bc_mask, missing, omega, steps=args.graph)
+        graph_lps = (_lib.launch_count() - c0) / (args.graph + 2)  # kernels per step (2 eager warm-up steps + the capture)
+        for _ in range(3):
+            graphed()
+        torch.cuda.synchronize()
+
     # ---- timed region: exactly K steps, CUDA events on the launching stream
     sampler = ClockSampler(local_rank)
     if rank == 0:
@@ -328,14 +342,21 @@ def run_native(args):
     ev1 = torch.cuda.Event(enable_timing=True)
     barrier()
     ev0.record()
-    for _ in range(args.steps):
-        f_0, f_1 = stepper(f_0, f_1, bc_mask, missing, omega, t)
-        f_0, f_1 = f_1, f_0
-        t += 1
+    if graphed is not None:
+        for _ in range(args.steps // args.graph):
+            graphed()
+        t += args.steps
+    else:
+        for _ in range(args.steps):
+            f_0, f_1 = stepper(f_0, f_1, bc_mask, missing, omega, t)
+            f_0, f_1 = f_1, f_0
+            t += 1
     ev1.record()
     barrier()
     ms = ev0.elapsed_time(ev1)
     launches = _lib.launch_count() - launches0
+    if graphed is not None:
+        launches = int(round(graph_lps * args.steps))  # kernels replayed from the graphs (no host-side launch calls)
     if world > 1:
         tt = torch.tensor([ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -352,13 +373,16 @@ def run_native(args):
         torch.cuda.synchronize()
         for a, b in evs:
             a.record()
-            f_0, f_1 = stepper(f_0, f_1, bc_mask, missing, omega, t)
+            if graphed is not None:
+                graphed()
+            else:
+                f_0, f_1 = stepper(f_0, f_1, bc_mask, missing, omega, t)
+                f_0, f_1 = f_1, f_0
             b.record()
-            f_0, f_1 = f_1, f_0
             t += 1
         torch.cuda.synchronize()
         per = sorted(a.elapsed_time(b) for a, b in evs)
-        k_ms = sum(per) / len(per)
+        k_ms = sum(per) / len(per) / (args.graph if graphed is not None else 1)
         bytes_per_launch = b_alg(vs.q, policy) * ncell
         achieved = bytes_per_launch / (k_ms * 1e-3) / 1e9
         roofline = {
@@ -415,6 +439,7 @@ def run_native(args):
         "config": {
             "workload": workload, "lattice": lattice, "collision": collision, "policy": policy, "shape": list(shape), "omega": omega,
             "decomposition": f"x-slab x{world}" if world > 1 else "single block",
+            **({"graph_steps": args.graph} if graphed is not None else {}),
             "l2": "inputs larger than L2 (two population buffers of %.1f GB each)" % (vs.q * ncell * STORE_BYTES[policy] / world / 1e9),
         },
         "gpu_launches": int(launches),
@@ -509,6 +534,7 @@ def main():
     ap.add_argument("--variant", type=int, default=0, help="kernel variant of xlb_step (0 auto, 2 vector, 3 generic, 4 bulk-staged)")
     ap.add_argument("--radius", type=int, default=None, help="override the obstacle radius of the sphere / wind-tunnel workloads (experiments only)")
     ap.add_argument("--shape", default=None, help="override the workload's shape, e.g. 48,1536,1536 (experiments only; config.shape reports it)")
+    ap.add_argument("--graph", type=int, default=0, help="replay the loop as CUDA graphs of this many (even) steps each (GraphedSteps); 0 = eager launches")
     ap.add_argument("--strong", action="store_true", help="N>1: keep the global shape of the workload (strong scaling) instead of one block per GPU")
     args = ap.parse_args()
     if args.workload is None:

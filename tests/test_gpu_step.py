@@ -390,3 +390,29 @@ def test_fp16_packed_kernel_bitwise_equals_generic(case):
     assert a.dtype == np.float16
     assert np.array_equal(a.view(np.uint16), b.view(np.uint16))
     assert rel_err(a, ref) <= TOL_ONE_STEP["FP32FP16"] * (4 if case["collision"] == "KBC" else 1)
+
+
+# ----------------------------------------------------------------------------- CUDA-graph replay of the step loop
+@pytest.mark.parametrize("case", [cases.cavity3d(16, omega=1.7), cases.sphere3d((48, 24, 24)), cases.cavity3d(16, policy="FP32FP16", omega=1.7)],
+                         ids=lambda c: c["name"])
+def test_graphed_steps_equal_eager_loop(case):
+    """GraphedSteps (an even number of steps captured into one CUDA graph) == the eager loop, bitwise, including the
+    two-launch steps of the BC cell list; replays go through no host-side library call."""
+    from xlb_b200.operator.stepper import GraphedSteps
+
+    st, _ = build_product(case, backend_config={"bc_cell_list": True})
+    f_0, f_1, bc_mask, missing = st.prepare_fields()
+    f_0.copy_(to_dev(cases.random_state(case, seed=9)))
+    g_0, g_1 = f_0.clone(), f_1.clone()
+    for i in range(12):
+        g_0, g_1 = st(g_0, g_1, bc_mask, missing, case["omega"], i)
+        g_0, g_1 = g_1, g_0
+    graphed = GraphedSteps(st, f_0, f_1, bc_mask, missing, case["omega"], steps=4)  # f_1 is scratch, f_0 is left as it was
+    n0 = _lib.launch_count()
+    for _ in range(3):
+        a, b = graphed()
+    assert _lib.launch_count() == n0  # replays issue no launches through the library's host path
+    assert a.data_ptr() == f_0.data_ptr()
+    assert torch.equal(a, g_0)
+    with pytest.raises(ValueError):
+        GraphedSteps(st, f_0, f_1, bc_mask, missing, case["omega"], steps=3)
