@@ -5,12 +5,21 @@
 #include "xlb_step.cuh"
 #include "xlb_step_bulk.cuh"
 #include "xlb_step_h2.cuh"
+#include "xlb_step_march.cuh"
 
 #ifndef XLB_Q
 #error "compile with -DXLB_Q -DXLB_TC -DXLB_TS -DXLB_TAG"
 #endif
 
 // tuning knobs (overridable from the command line for sweeps; see tools/sweep.py)
+// 1: the FP16-storage instances run step_march_h2_kernel (register double buffering along x, xlb_step_march.cuh) with
+// XLB_TUNE_XC planes per thread; experimental, see profiles/sweep13_f16_march.log
+#ifndef XLB_TUNE_MARCH
+#define XLB_TUNE_MARCH 0
+#endif
+#ifndef XLB_TUNE_XC
+#define XLB_TUNE_XC 16
+#endif
 // 1: FP32-compute / FP16-store instances run step_vector_h2_kernel (populations packed as half2 from load to store)
 #ifndef XLB_TUNE_H2
 #define XLB_TUNE_H2 1
@@ -50,7 +59,10 @@ static int launch_vector(const StepParams& p0, cudaStream_t st) {
 #else
     constexpr int MINB = (V == 1) ? 4 : default_minb<S, Q, V>();
 #endif
-    if constexpr (USE_H2) {
+    if constexpr (USE_H2 && XLB_TUNE_MARCH) {
+        dim3 mgrid(grid.x, (unsigned)((p.x_end - p.x_begin + XLB_TUNE_XC - 1) / XLB_TUNE_XC), 1);
+        step_march_h2_kernel<Q, COLL, V, BLOCK, MINB, HAS_BC, HALF, XLB_TUNE_XC><<<mgrid, BLOCK, 0, st>>>(p);
+    } else if constexpr (USE_H2) {
         step_vector_h2_kernel<Q, COLL, V, BLOCK, MINB, HAS_BC, HALF><<<grid, BLOCK, 0, st>>>(p);
     } else {
         step_vector_kernel<T, S, Q, COLL, V, BLOCK, MINB, HAS_BC, HALF><<<grid, BLOCK, 0, st>>>(p);
