@@ -42,6 +42,7 @@ WORKLOADS = {
     "cavity384x256x512_d3q27_bgk_fp32": ("D3Q27", "BGK", "FP32FP32", (384, 256, 512), 1.7, "cavity"),
     "cavity768x256x256_d3q27_kbc_fp32": ("D3Q27", "KBC", "FP32FP32", (768, 256, 256), 1.6, "cavity"),
     "cavity768_d3q19_bgk_fp16": ("D3Q19", "BGK", "FP32FP16", (512, 768, 768), 1.0, "cavity"),
+    "cavity512_d3q19_bgk_fp16": ("D3Q19", "BGK", "FP32FP16", (512, 512, 512), 1.0, "cavity"),
     "cavity1024_d3q19_bgk_fp16": ("D3Q19", "BGK", "FP32FP16", (1024, 1024, 1024), 1.0, "cavity"),
     "cavity640_d3q19_bgk_fp16": ("D3Q19", "BGK", "FP32FP16", (640, 640, 640), 1.0, "cavity"),
     # BASELINE configs[4] (windtunnel_3d.py with a sphere instead of the STL car): 1536 x 1536 cross-section,
@@ -130,7 +131,7 @@ class ClockSampler:
 
 
 # --------------------------------------------------------------------------- case construction (product objects)
-def build_case(workload, slab=None, shape=None, variant=0, radius=None):
+def build_case(workload, slab=None, shape=None, variant=0, radius=None, backend_config=None):
     """Product-side objects of a workload.  BC index sets are generated per slab (global coords) so that the
     1536^3-class cases never materialise a global index list on one rank."""
     import numpy as np
@@ -187,22 +188,90 @@ def build_case(workload, slab=None, shape=None, variant=0, radius=None):
             ExtrapolationOutflowBC(indices=box_ne["right"]),
             HalfwayBounceBackBC(indices=sphere),
         ]
-    stepper = IncompressibleNavierStokesStepper(grid=grid, boundary_conditions=bcs, collision_type=collision, backend_config={"kernel_variant": variant})
+    cfg = {"kernel_variant": variant}
+    cfg.update(backend_config or {})
+    stepper = IncompressibleNavierStokesStepper(grid=grid, boundary_conditions=bcs, collision_type=collision, backend_config=cfg)
     return stepper, vs, pol, shape, omega
 
 
 # --------------------------------------------------------------------------- CPU legs (the only users of oracle/)
+def host_threads():
+    """Host threads this process may use (torchrun exports OMP_NUM_THREADS=1, which is not the box's core count)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
+def probe_reference_jax():
+    """SURVEY 8(c) "extra safety" / BASELINE.md 3(2a): is the real reference (xlb on JAX / XLA:CPU) runnable on this box?
+    Returns (module or None, one-line reason).  ``baseline/_ref`` is where an offline install of the reference would live."""
+    ref_dir = os.path.join(ROOT, "baseline", "_ref")
+    if os.path.isdir(ref_dir) and ref_dir not in sys.path:
+        sys.path.append(ref_dir)
+    try:
+        import jax  # noqa: F401
+    except Exception as exc:  # ModuleNotFoundError on this image (no jax wheel in /opt/wheelhouse)
+        return None, f"not importable ({type(exc).__name__}: {exc})"
+    try:
+        import xlb as ref_xlb  # the unmodified reference package, if it was installed into baseline/_ref
+    except Exception as exc:
+        return None, f"jax imports but the reference package does not ({type(exc).__name__}: {exc})"
+    return ref_xlb, "importable"
+
+
+def reference_jax_cavity(ref_xlb, n, omega, budget_s, max_steps):
+    """The reference's own mlups_3d.py loop (examples/performance/mlups_3d.py:177-262) on its JAX backend, CPU devices,
+    with block_until_ready for honest timing.  Only reached when ``probe_reference_jax`` found jax + xlb on this box."""
+    import jax
+    import numpy as np
+    from xlb.compute_backend import ComputeBackend
+    from xlb.grid import grid_factory
+    from xlb.operator.boundary_condition import EquilibriumBC, FullwayBounceBackBC
+    from xlb.operator.stepper import IncompressibleNavierStokesStepper
+    from xlb.precision_policy import PrecisionPolicy
+
+    vs = ref_xlb.velocity_set.D3Q19(precision_policy=PrecisionPolicy.FP32FP32, compute_backend=ComputeBackend.JAX)
+    ref_xlb.init(velocity_set=vs, default_backend=ComputeBackend.JAX, default_precision_policy=PrecisionPolicy.FP32FP32)
+    grid = grid_factory((n, n, n), compute_backend=ComputeBackend.JAX)
+    box = grid.bounding_box_indices()
+    box_ne = grid.bounding_box_indices(remove_edges=True)
+    walls = [box["bottom"][i] + box["left"][i] + box["right"][i] + box["front"][i] + box["back"][i] for i in range(3)]
+    walls = np.unique(np.array(walls), axis=-1).tolist()
+    bcs = [EquilibriumBC(rho=1.0, u=(0.02, 0.0, 0.0), indices=box_ne["top"]), FullwayBounceBackBC(indices=walls)]
+    st = IncompressibleNavierStokesStepper(grid=grid, boundary_conditions=bcs, collision_type="BGK")
+    f_0, f_1, bc_mask, missing = st.prepare_fields()
+    f_0, f_1 = st(f_0, f_1, bc_mask, missing, omega, 0)
+    f_0, f_1 = f_1, f_0
+    jax.block_until_ready(f_0)
+    t0 = time.perf_counter()
+    steps = 0
+    while steps < max_steps and (time.perf_counter() - t0) < budget_s:
+        f_0, f_1 = st(f_0, f_1, bc_mask, missing, omega, steps + 1)
+        f_0, f_1 = f_1, f_0
+        jax.block_until_ready(f_0)
+        steps += 1
+    return steps, time.perf_counter() - t0, jax.device_count()
+
+
 def cpu_baseline(workload, budget_s=20.0, max_steps=8):
-    """The oracle port of the reference's JAX step (nse_stepper.py:238-282), timed on this box's host cores on a bounded
-    sample: the same BCs / lattice / policy at 128^3 (BASELINE config 1 when the workload is the cavity).  The cavity
-    runs the multi-threaded torch-CPU transcription of the oracle (all host threads, like XLA:CPU would use); the
-    other workloads run the single-threaded NumPy oracle."""
+    """The reference's CPU path for this workload, timed on this box's host cores on a bounded sample: the same BCs /
+    lattice / policy at 128^3 (BASELINE configs[0] when the workload is the cavity).  Order of preference: the real
+    reference on JAX / XLA:CPU (kind "reference") when jax and the reference package import here; else the oracle port of
+    nse_stepper.py:238-282 (kind "port") -- for the cavity the multi-threaded torch-CPU transcription of the oracle on all
+    host threads (what XLA:CPU would use), for the other workloads the single-threaded NumPy oracle."""
     import numpy as np
     import torch
 
     from oracle import cases
 
     lattice, collision, policy, shape, omega, kind = WORKLOADS[workload]
+    ref_xlb, jax_note = probe_reference_jax()
+    if ref_xlb is not None and kind == "cavity" and lattice == "D3Q19" and collision == "BGK" and policy == "FP32FP32":
+        steps, dt, ndev = reference_jax_cavity(ref_xlb, 128, omega, budget_s, max_steps)
+        return {"value": 128**3 * steps / dt / 1e6, "unit": UNIT, "cores": host_threads(), "kind": "reference", "jax": jax_note,
+                "sample": f"{steps} steps of the reference's mlups_3d.py loop at 128^3 on JAX / XLA:CPU ({ndev} device(s))", "seconds": dt,
+                "steps": steps, "sample_shape": [128, 128, 128]}
     if kind == "cavity":
         case = cases.cavity3d(128, policy=policy, lattice=lattice, collision=collision, omega=omega)
     else:
@@ -216,6 +285,7 @@ def cpu_baseline(workload, budget_s=20.0, max_steps=8):
     if kind == "cavity" and collision == "BGK":
         from oracle.torch_cpu import TorchCavityStepper, to_torch
 
+        torch.set_num_threads(host_threads())  # torchrun sets OMP_NUM_THREADS=1 for its workers
         step = TorchCavityStepper(st)
         f0, bc = to_torch(f0), to_torch(bc)
         cores, how = torch.get_num_threads(), f"torch-CPU transcription of the oracle, {torch.get_num_threads()} threads"
@@ -233,14 +303,21 @@ def cpu_baseline(workload, budget_s=20.0, max_steps=8):
         "unit": UNIT,
         "cores": cores,
         "kind": "port",
+        "jax": jax_note,
         "sample": f"{steps} steps of {case['name']} ({ncell} cells), {how}; oracle port of nse_stepper.py:238-282; host has {os.cpu_count()} cores",
         "seconds": dt,
         "steps": steps,
+        "sample_shape": list(case["shape"]),
     }
 
 
+CPU_KEYS = ("value", "unit", "cores", "kind", "sample", "sample_shape", "jax")
+
+
 def run_reference(args):
-    """--impl reference: the reference's CPU path (oracle port; the reference itself needs jax, absent here)."""
+    """--impl reference: the reference's CPU path on this box's host cores (the real JAX backend when it imports here,
+    else the oracle port), on a bounded sample of the workload.  ``config.shape`` is the shape that actually ran;
+    ``config.sample_of`` names the workload's full shape."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
@@ -261,8 +338,9 @@ def run_reference(args):
         "vs_baseline": None,
         "dtype": DTYPE_NAME[policy],
         "data": "synthetic",
-        "config": {"workload": workload, "lattice": lattice, "collision": collision, "policy": policy, "shape": list(shape), "omega": omega},
-        "cpu_baseline": {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "config": {"workload": workload, "lattice": lattice, "collision": collision, "policy": policy, "shape": base["sample_shape"],
+                   "sample_of": list(shape), "omega": omega, "host_threads": base["cores"]},
+        "cpu_baseline": {k: base[k] for k in CPU_KEYS},
         "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -272,6 +350,136 @@ def run_reference(args):
 
 
 # --------------------------------------------------------------------------- native arm
+def time_steps(stepper, fields, omega, steps, warmup, graph=0, t0=0):
+    """``warmup`` untimed steps, then ``steps`` timed ones between two CUDA events on the launching stream.
+    Returns (ms per step, kernels launched per step, fields).  ``graph`` > 0 replays GraphedSteps of that many steps."""
+    import torch
+
+    from xlb_b200 import _lib
+
+    f_0, f_1, bc_mask, missing = fields
+    t = t0
+    for _ in range(warmup):
+        f_0, f_1 = stepper(f_0, f_1, bc_mask, missing, omega, t)
+        f_0, f_1 = f_1, f_0
+        t += 1
+    graphed = None
+    if graph:
+        from xlb_b200.operator.stepper import GraphedSteps
+
+        steps = max(graph, steps // graph * graph)
+        c0 = _lib.launch_count()
+        graphed = GraphedSteps(stepper, f_0, f_1, bc_mask, missing, omega, steps=graph)
+        lps = (_lib.launch_count() - c0) / (graph + 2)
+        for _ in range(3):
+            graphed()
+    torch.cuda.synchronize()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    c0 = _lib.launch_count()
+    ev0.record()
+    if graphed is not None:
+        for _ in range(steps // graph):
+            graphed()
+    else:
+        for _ in range(steps):
+            f_0, f_1 = stepper(f_0, f_1, bc_mask, missing, omega, t)
+            f_0, f_1 = f_1, f_0
+            t += 1
+    ev1.record()
+    torch.cuda.synchronize()
+    if graphed is None:
+        lps = (_lib.launch_count() - c0) / steps
+    return ev0.elapsed_time(ev1) / steps, lps, (f_0, f_1, bc_mask, missing)
+
+
+# the other BASELINE configs, timed in the same run as the headline (VERDICT r1 item 2): name -> (workload, shape or None, steps, graph)
+EXTRA_CONFIGS = [
+    ("C1_cavity128_d3q19_bgk_fp32_eager", "cavity128_d3q19_bgk_fp32", None, 400, 0),
+    ("C1_cavity128_d3q19_bgk_fp32_graph20", "cavity128_d3q19_bgk_fp32", None, 400, 20),
+    ("C2_cavity512_d3q19_bgk_fp64", "cavity512_d3q19_bgk_fp64", None, 20, 0),
+    ("C3_sphere384x128x128_d3q27_kbc_fp32", "sphere384_d3q27_kbc_fp32", None, 200, 0),
+    ("C3_sphere384x128x128_d3q27_kbc_fp32_graph20", "sphere384_d3q27_kbc_fp32", None, 200, 20),
+    ("sphere768x256x256_d3q27_kbc_fp32", "sphere768_d3q27_kbc_fp32", None, 40, 0),
+    ("cavity384x256x512_d3q27_bgk_fp32", "cavity384x256x512_d3q27_bgk_fp32", None, 40, 0),
+    ("C4block_cavity512x768x768_d3q19_bgk_fp16", "cavity768_d3q19_bgk_fp16", None, 20, 0),
+    ("C5block_windtunnel192x1536x1536_d3q27_kbc_fp32", "windtunnel192x1536x1536_d3q27_kbc_fp32", None, 10, 0),
+]
+
+
+def run_extra_configs(peak, budget_s=150.0):
+    """MLUPS / kernel time / roofline fraction of the other single-GPU BASELINE configurations (device-timed like the
+    headline: CUDA events around the step loop, inputs larger than L2 except the 128^3 case, which says so)."""
+    import torch
+
+    out = {}
+    t_start = time.perf_counter()
+    for name, workload, shape, steps, graph in EXTRA_CONFIGS:
+        if time.perf_counter() - t_start > budget_s:
+            out[name] = {"skipped": "time budget of the configs block used up"}
+            continue
+        lattice, collision, policy, shape0, omega, kind = WORKLOADS[workload]
+        try:
+            stepper, vs, pol, shp, omega = build_case(workload, shape=shape)
+            fields = stepper.prepare_fields()
+            ms, lps, fields = time_steps(stepper, fields, omega, steps, 5, graph=graph)
+            ncell = shp[0] * shp[1] * shp[2]
+            bpc = b_alg(vs.q, policy)
+            gbs = bpc * ncell / (ms * 1e-3) / 1e9
+            out[name] = {
+                "workload": workload, "shape": list(shp), "lattice": lattice, "collision": collision, "policy": policy,
+                "mlups": ncell / (ms * 1e-3) / 1e6, "kernel_ms": ms, "achieved_gbs": gbs, "frac": gbs / peak, "bytes_per_cell": bpc,
+                "launches_per_step": lps, "steps": steps, **({"graph_steps": graph} if graph else {}),
+                "finite": bool(torch.isfinite(fields[0].float().sum()).item()),
+                **({"l2": "working set (2 x 159 MB) is of the order of the 126 MB L2"} if ncell <= 128**3 else {}),
+            }
+            del stepper, fields
+        except Exception as exc:  # a config that cannot run (e.g. memory) must not take the headline line down
+            out[name] = {"error": f"{type(exc).__name__}: {exc}"[:300]}
+        torch.cuda.empty_cache()
+    return out
+
+
+def nrank_bitwise_check(workload, slab, world, steps=5):
+    """N-rank == 1-rank, bitwise (SURVEY 8(e) correctness check), inside the bench so that the driver's scaling run carries
+    the proof: a small global block of the same workload family is stepped ``steps`` times on the slab stepper (all ranks,
+    halo ring, overlap schedule) and, redundantly on every rank, as one block; the gathered slabs must equal it exactly."""
+    import torch
+
+    from xlb_b200.distribute import distribute
+
+    lattice, collision, policy, shape0, omega, kind = WORKLOADS[workload]
+    gshape = (6 * world + 1, 40, 128)  # uneven slabs (remainder plane on rank 0)
+    single, vs, _, _, omega = build_case(workload, shape=gshape)
+    s_0, s_1, s_bc, s_mm = single.prepare_fields()
+    gen = torch.Generator(device="cpu")
+    gen.manual_seed(1234)
+    noise = torch.rand((vs.q,) + gshape, generator=gen, dtype=torch.float32)
+    w = torch.tensor(vs.w, dtype=torch.float32).reshape(-1, 1, 1, 1)
+    init = (w * (1.0 + 0.01 * (2.0 * noise - 1.0))).to(s_0.dtype).cuda()
+    s_0.copy_(init)
+    part, _, _, _, _ = build_case(workload, slab=slab, shape=gshape)
+    dstep = distribute(part, part.grid, vs)
+    p_0, p_1, p_bc, p_mm = dstep.prepare_fields()
+    x0, n = slab.local_range(gshape[0])
+    p_0[:, 1 : n + 1].copy_(init[:, x0 : x0 + n])
+    dstep.halo.exchange(p_0)
+    torch.cuda.synchronize()
+    for t in range(steps):
+        s_0, s_1 = single(s_0, s_1, s_bc, s_mm, omega, t)
+        s_0, s_1 = s_1, s_0
+        p_0, p_1 = dstep(p_0, p_1, p_bc, p_mm, omega, t)
+        p_0, p_1 = p_1, p_0
+    torch.cuda.synchronize()
+    same = bool(torch.equal(dstep.gather(p_0), s_0)) and bool(torch.equal(dstep.gather(p_bc), s_bc))
+    mode = "peer push" if dstep.peer is not None else "nccl send/recv"
+    dstep.close()
+    flag = torch.tensor([1 if same else 0], device="cuda")
+    import torch.distributed as dist
+
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    return bool(flag.item()), {"global_shape": list(gshape), "steps": steps, "workload_family": workload, "halo": mode}
+
+
 def run_native(args):
     import torch
     import torch.distributed as dist
@@ -292,32 +500,47 @@ def run_native(args):
 
         slab = SlabDecomposition(rank=rank, world=world)
 
-    workload = args.workload
-    lattice, collision, policy, shape, omega, kind = WORKLOADS[workload]
-    if args.shape:
-        shape = tuple(int(v) for v in args.shape.split(","))
-    if world > 1 and not args.strong:
-        shape = (shape[0] * world,) + tuple(shape[1:])  # weak scaling: the N=1 block per GPU, stacked along x
-    stepper, vs, pol, shape, omega = build_case(workload, slab=slab, shape=shape, variant=args.variant, radius=args.radius)
-    if slab is not None:
-        from xlb_b200.distribute import distribute
-
-        stepper = distribute(stepper, stepper.grid, vs, overlap=not args.no_overlap)
-    f_0, f_1, bc_mask, missing = stepper.prepare_fields()
-    ncell = shape[0] * shape[1] * shape[2]
-
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- warm-up
-    t = 0
-    for _ in range(max(args.warmup, 3)):
-        f_0, f_1 = stepper(f_0, f_1, bc_mask, missing, omega, t)
-        f_0, f_1 = f_1, f_0
-        t += 1
-    barrier()
+    def max_over_ranks(ms):
+        if world > 1:
+            tt = torch.tensor([ms], device="cuda", dtype=torch.float64)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            return float(tt.item())
+        return ms
+
+    def timed_run(workload, shape, strong, steps, warmup):
+        """Build, warm up, time exactly ``steps`` steps (barrier + synchronize on both sides, CUDA events, max over ranks)."""
+        lattice, collision, policy, shape0, omega, kind = WORKLOADS[workload]
+        shape = tuple(shape) if shape else shape0
+        if world > 1 and not strong:
+            shape = (shape[0] * world,) + tuple(shape[1:])  # weak scaling: the N=1 block per GPU, stacked along x
+        stepper, vs, pol, shape, omega = build_case(workload, slab=slab, shape=shape, variant=args.variant, radius=args.radius)
+        if slab is not None:
+            from xlb_b200.distribute import distribute
+
+            stepper = distribute(stepper, stepper.grid, vs, overlap=not args.no_overlap, graph=not args.no_dist_graph, halo=args.halo)
+        f_0, f_1, bc_mask, missing = stepper.prepare_fields()
+        t = 0
+        for _ in range(warmup):
+            f_0, f_1 = stepper(f_0, f_1, bc_mask, missing, omega, t)
+            f_0, f_1 = f_1, f_0
+            t += 1
+        barrier()
+        return dict(stepper=stepper, vs=vs, policy=policy, shape=shape, omega=omega, fields=(f_0, f_1, bc_mask, missing), t=t,
+                    lattice=lattice, collision=collision, ncell=shape[0] * shape[1] * shape[2])
+
+    workload = args.workload
+    shape_arg = tuple(int(v) for v in args.shape.split(",")) if args.shape else None
+    warmup = max(args.warmup, 3)
+    run = timed_run(workload, shape_arg, args.strong, args.steps, warmup)
+    stepper, vs, policy, shape, omega, ncell = run["stepper"], run["vs"], run["policy"], run["shape"], run["omega"], run["ncell"]
+    lattice, collision = run["lattice"], run["collision"]
+    f_0, f_1, bc_mask, missing = run["fields"]
+    t = run["t"]
 
     # ---- optional: replay the step loop as CUDA graphs of --graph steps each (launch-bound small lattices)
     graphed, graph_lps = None, None
@@ -353,14 +576,12 @@ def run_native(args):
             t += 1
     ev1.record()
     barrier()
-    ms = ev0.elapsed_time(ev1)
+    ms = max_over_ranks(ev0.elapsed_time(ev1))
     launches = _lib.launch_count() - launches0
     if graphed is not None:
         launches = int(round(graph_lps * args.steps))  # kernels replayed from the graphs (no host-side launch calls)
-    if world > 1:
-        tt = torch.tensor([ms], device="cuda", dtype=torch.float64)
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        ms = float(tt.item())
+    elif world > 1 and getattr(stepper, "launches_per_step", None):
+        launches = int(round(stepper.launches_per_step * args.steps))  # replayed from the distributed step's CUDA graph
     clocks = sampler.stop() if rank == 0 else None
     mlups = ncell * args.steps / (ms * 1e-3) / 1e6
     finite = bool(torch.isfinite(f_0.float().sum()).item())
@@ -385,6 +606,7 @@ def run_native(args):
         k_ms = sum(per) / len(per) / (args.graph if graphed is not None else 1)
         bytes_per_launch = b_alg(vs.q, policy) * ncell
         achieved = bytes_per_launch / (k_ms * 1e-3) / 1e9
+        traffic = ncu_traffic(workload, args.variant)
         roofline = {
             "bound": "hbm",
             "kernel": {0: "xlb_step (auto variant)", 2: "step_vector_kernel", 3: "step_generic_kernel", 4: "step_bulk_kernel"}.get(args.variant, "xlb_step"),
@@ -392,7 +614,8 @@ def run_native(args):
             "peak": peak,
             "unit": "GB/s",
             "frac": achieved / peak,
-            "traffic": ncu_traffic(workload, args.variant),
+            "traffic": traffic,
+            "traffic_source": "committed ncu --set full capture (profiles/ncu_traffic.json), not re-measured in this run" if traffic else None,
             "frac_of_nominal_8000": achieved / 8000.0,
             "bytes_per_launch": bytes_per_launch,
             "bytes_per_cell": b_alg(vs.q, policy),
@@ -403,21 +626,67 @@ def run_native(args):
         }
 
     if world > 1:
-        # per-GPU roofline of the whole distributed step (two edge-plane launches + interior launch + halo ring):
+        # per-GPU roofline of the whole distributed step (edge-plane launch + interior launch + halo ring):
         # algorithmic bytes of one rank's slab over the max-over-ranks step time
         per_rank = b_alg(vs.q, policy) * (ncell // world)
         achieved = per_rank / (ms / args.steps * 1e-3) / 1e9
         roofline = {
-            "bound": "hbm", "kernel": "per-GPU slab step (2 edge-plane launches + interior launch, halo exchange overlapped)",
+            "bound": "hbm", "kernel": "per-GPU slab step (edge-plane launch + interior launch, halo exchange overlapped)",
             "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
             "frac_of_nominal_8000": achieved / 8000.0, "bytes_per_launch": per_rank, "bytes_per_cell": b_alg(vs.q, policy),
             "cells_per_launch": ncell // world, "kernel_ms": ms / args.steps, "peak_source": peak_src,
         }
 
     # ---- e2e: HOST buffers in, HOST buffers out (pinned), copies inside the timed region
-    e2e = None
+    e2e = e2e_resident = None
     if world == 1 and not args.no_e2e:
         e2e = run_e2e(stepper, f_0, f_1, bc_mask, missing, omega, t, ncell, max(1, min(args.steps, args.e2e_steps)))
+        e2e_resident = run_resident_api(stepper, f_0, f_1, bc_mask, missing, omega, t, ncell, min(args.steps, 20))
+
+    # ---- the rest of the BASELINE metric on the same clock
+    extra = {}
+    halo_mode = None
+    if world > 1:
+        halo_mode = "peer push fused into the edge-plane launch (CUDA IPC over NVLink)" if stepper.peer is not None else "NCCL send/recv on a communication stream"
+        if stepper.peer is not None and stepper.peer.timed_out():
+            raise RuntimeError("a halo wait timed out during the timed region")
+        stepper.close()
+    del f_0, f_1, bc_mask, missing, stepper, graphed
+    run.clear()
+    torch.cuda.empty_cache()
+    if world == 1 and not args.no_configs:
+        extra["configs"] = run_extra_configs(peak)
+    if world > 1 and not args.no_configs:
+        ok, info = nrank_bitwise_check(workload, slab, world)
+        extra["nrank_bitwise"] = ok
+        extra["nrank_bitwise_case"] = info
+        torch.cuda.empty_cache()
+        if not args.strong:
+            # BASELINE configs[3]: 1024^3 D3Q19 BGK FP32FP16, strong scaling (global shape fixed, slabs shrink with N)
+            sw = "cavity1024_d3q19_bgk_fp16"
+            srun = timed_run(sw, None, True, args.steps, warmup)
+            st2, (g_0, g_1, g_bc, g_mm), t2 = srun["stepper"], srun["fields"], srun["t"]
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier()
+            e0.record()
+            for _ in range(args.steps):
+                g_0, g_1 = st2(g_0, g_1, g_bc, g_mm, srun["omega"], t2)
+                g_0, g_1 = g_1, g_0
+                t2 += 1
+            e1.record()
+            barrier()
+            sms = max_over_ranks(e0.elapsed_time(e1))
+            per_rank = b_alg(19, "FP32FP16") * (srun["ncell"] // world)
+            extra["strong"] = {
+                "workload": sw, "shape": list(srun["shape"]), "scaling": "strong", "n_gpus": world, "steps": args.steps,
+                "mlups": srun["ncell"] * args.steps / (sms * 1e-3) / 1e6, "ms_per_step": sms / args.steps,
+                "per_gpu_frac": per_rank / (sms / args.steps * 1e-3) / 1e9 / peak,
+                "finite": bool(torch.isfinite(g_0.float().sum()).item()),
+            }
+            st2.close()
+            del st2, g_0, g_1, g_bc, g_mm
+            srun.clear()
+            torch.cuda.empty_cache()
 
     if rank != 0:
         if world > 1:
@@ -429,7 +698,7 @@ def run_native(args):
         "unit": UNIT,
         "n_gpus": world,
         "steps": args.steps,
-        "warmup": max(args.warmup, 3),
+        "warmup": warmup,
         "ms_per_step": ms / args.steps,
         "higher_is_better": True,
         "scaling": "strong" if (world > 1 and args.strong) else "weak",
@@ -439,7 +708,8 @@ def run_native(args):
         "config": {
             "workload": workload, "lattice": lattice, "collision": collision, "policy": policy, "shape": list(shape), "omega": omega,
             "decomposition": f"x-slab x{world}" if world > 1 else "single block",
-            **({"graph_steps": args.graph} if graphed is not None else {}),
+            **({"halo": halo_mode} if halo_mode else {}),
+            **({"graph_steps": args.graph} if args.graph and world == 1 else {}),
             "l2": "inputs larger than L2 (two population buffers of %.1f GB each)" % (vs.q * ncell * STORE_BYTES[policy] / world / 1e9),
         },
         "gpu_launches": int(launches),
@@ -450,10 +720,11 @@ def run_native(args):
         line["roofline"] = roofline
     if e2e:
         line["e2e"] = e2e
-        line["e2e_resident_api"] = run_resident_api(stepper, f_0, f_1, bc_mask, missing, omega, t, ncell, min(args.steps, 20))
+        line["e2e_resident_api"] = e2e_resident
+    line.update(extra)
     if world == 1 and not args.no_cpu_baseline:
         base = cpu_baseline(workload)
-        line["cpu_baseline"] = {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        line["cpu_baseline"] = {k: base[k] for k in CPU_KEYS}
     _STDOUT.write(json.dumps(line) + "\n")
     _STDOUT.flush()
     if world > 1:
@@ -531,6 +802,9 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-overlap", action="store_true")
+    ap.add_argument("--halo", default="auto", choices=["auto", "peer", "nccl"], help="N>1: halo exchange fused into the edge launch over peer memory, or NCCL send/recv")
+    ap.add_argument("--no-dist-graph", action="store_true", help="N>1: issue the distributed step eagerly instead of replaying its CUDA graph")
+    ap.add_argument("--no-configs", action="store_true", help="skip the extra BASELINE configs block (N=1) / the bitwise check and the strong-scaling line (N>1)")
     ap.add_argument("--variant", type=int, default=0, help="kernel variant of xlb_step (0 auto, 2 vector, 3 generic, 4 bulk-staged)")
     ap.add_argument("--radius", type=int, default=None, help="override the obstacle radius of the sphere / wind-tunnel workloads (experiments only)")
     ap.add_argument("--shape", default=None, help="override the workload's shape, e.g. 48,1536,1536 (experiments only; config.shape reports it)")

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define XLB_B200_ABI_VERSION 3
+#define XLB_B200_ABI_VERSION 4
 
 /* element types (xlb/precision_policy.py:13-54) */
 enum { XLB_F16 = 0, XLB_F32 = 1, XLB_F64 = 2, XLB_U8 = 3 };
@@ -88,6 +88,27 @@ typedef struct XlbCollisionParams {
     int64_t n_bc_cells;      /* entries of bc_cells */
 } XlbCollisionParams;
 
+/* Which planes (and, for the 2-D slab decomposition, which rows of each plane) one launch updates: planes
+ * x_begin + k * x_stride (k < n_planes), rows y_begin + k * y_stride (k < n_rows).  n_rows == 0 means every row.
+ * A stride lets ONE launch update the two edge planes of a slab (x_begin = first owned, x_stride = owned - 1, n_planes = 2). */
+typedef struct XlbStepRange {
+    int32_t x_begin, x_stride, n_planes;
+    int32_t y_begin, y_stride, n_rows;
+} XlbStepRange;
+
+/* Halo push: the peer-memory half of the multi-GPU step (xlb/distribute/distribute.py:23-44, the lax.ppermute ring).
+ * While the step kernel updates slab-axis coordinate src[k] (the first owned plane for k = 0, the last owned plane for k = 1;
+ * planes of a 3-D block, rows of a D2Q9 block) it stores the populations that cross that side of the slab (c = -1 for k = 0,
+ * c = +1 for k = 1 along the slab axis: velocity_set.left_indices / right_indices) ALSO into the ring neighbour's f1 buffer --
+ * a device pointer of another GPU mapped into this process (xlb_ipc_import), same layout and q_stride as f1 -- at its ghost
+ * plane / row dst[k].  Compute and transfer are one kernel: the NVLink stores are posted while the rest of the slab is being
+ * updated; no pack buffer, no collective call.  Ordering between ranks is the caller's (xlb_halo_signal / xlb_halo_wait). */
+typedef struct XlbHaloPush {
+    void* peer_f1[2];   /* [0] left neighbour's f1, [1] right neighbour's f1; NULL = no push on that side */
+    int32_t src[2];     /* my plane (row) whose outgoing populations are pushed: first owned, last owned */
+    int32_t dst[2];     /* the neighbour's ghost plane (row) that receives them: its right ghost, its left ghost */
+} XlbHaloPush;
+
 const char* xlb_last_error(void);
 int xlb_abi_version(void);
 int xlb_bc_entry_size(void);
@@ -107,6 +128,39 @@ int xlb_step(const XlbDomain* dom, int collision, const void* f0, void* f1, cons
 int xlb_step_ex(const XlbDomain* dom, int collision, const XlbCollisionParams* cp, const void* f0, void* f1, const uint8_t* bc_mask,
                 const uint8_t* missing_mask, const XlbBcEntry* bc_table, int n_bc, double omega, int timestep, int x_begin, int x_end,
                 int variant, void* stream);
+
+/* The general form of the step: the planes / rows of ``range`` (NULL = the whole block), optionally with the halo push of the
+ * outgoing edge populations into the ring neighbours' buffers (``halo``, may be NULL).  With cp->bc_cells the list must cover
+ * planes [x_begin, x_begin + (n_planes-1)*x_stride]; entries outside the launch's planes / rows are skipped. */
+int xlb_step_range(const XlbDomain* dom, int collision, const XlbCollisionParams* cp, const XlbStepRange* range, const XlbHaloPush* halo,
+                   const void* f0, void* f1, const uint8_t* bc_mask, const uint8_t* missing_mask, const XlbBcEntry* bc_table, int n_bc,
+                   double omega, int timestep, int variant, void* stream);
+
+/* Rank-to-rank ordering of the halo push, as two one-thread kernels on the caller's stream (capturable in a CUDA graph).
+ * Every rank owns a monotonic 64-bit flag per side, written by that side's neighbour, and two local counters.
+ *   xlb_halo_signal: ++*sent; store *sent to the two neighbours' flags (system-scope release after a system fence) -- enqueue it
+ *                    right after the edge launch: "my push number *sent has landed in your ghost planes";
+ *   xlb_halo_wait  : spin until both of MY flags are >= waited[0], then ++waited[0] -- enqueue it before the next edge launch
+ *                    (step 0 passes at once: the ghost planes of the initial state are filled by the setup exchange).
+ *                    ``waited`` points at TWO words: waited[1] stays 0 unless a neighbour's signal did not arrive within 30 s,
+ *                    in which case the kernel gives up (the GPU is never left spinning) and stores the missed epoch there.
+ * The wait of step t+1 also orders the NEXT push after the neighbour's last read of the ghost planes it overwrites, because a
+ * neighbour signals only after its own edge launch of step t has finished. */
+int xlb_halo_signal(uint64_t* sent, uint64_t* left_neighbours_flag, uint64_t* right_neighbours_flag, void* stream);
+int xlb_halo_wait(uint64_t* waited, const uint64_t* flag_from_left, const uint64_t* flag_from_right, void* stream);
+
+/* Peer mapping of device memory between the per-GPU processes of one node (CUDA IPC; the plumbing under XlbHaloPush).
+ * export: ``handle`` receives the 64-byte cudaIpcMemHandle_t of the allocation that contains ``dptr`` and ``*offset`` the byte
+ * offset of ``dptr`` inside it.  import: maps the allocation into this process (peer access enabled lazily) and returns
+ * base + offset in ``*dptr`` and the mapping's base in ``*base`` (one import per distinct handle; close with xlb_ipc_close). */
+int xlb_ipc_export(const void* dptr, void* handle, int64_t* offset);
+int xlb_ipc_import(const void* handle, int64_t offset, void** dptr, void** base);
+int xlb_ipc_close(void* base);
+
+/* Strided batch copy on ``stream``: ``n_runs`` runs of ``run_bytes`` contiguous bytes, run r from src + r * src_stride_bytes to
+ * dst + r * dst_stride_bytes, in any direction (host memory should be pinned).  One call moves an x-chunk of all q populations
+ * between a host lattice and a device staging block (HostStreamedStepper) instead of q separate copies. */
+int xlb_copy_runs(void* dst, int64_t dst_stride_bytes, const void* src, int64_t src_stride_bytes, int64_t run_bytes, int n_runs, void* stream);
 
 /* Compacts the cells of planes [x_begin, x_end) whose bc id maps to a kind in ``kind_mask`` (OR of 1 << XLB_BC_*; 0 = the kinds
  * XlbCollisionParams.bc_cells is meant for) into ``cells`` (linear indices (x*ny + y)*nz + z in no particular order, capacity ``capacity``

@@ -64,6 +64,40 @@ def test_halo_ring_gloo(world, lattice, shape, tmp_path):
     assert all((tmp_path / f"ok{r}").exists() for r in range(world))
 
 
+def _worker_2d(rank, world, port, shape, out_dir):
+    """D2Q9 slabs: ghost ROWS of a [q, n+2, ny] field (examples/cfd/lid_driven_cavity_2d_distributed.py:22)."""
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from xlb_b200.distribute import HaloExchange, SlabDecomposition
+
+        lat = make_lattice("D2Q9")
+        f = np.random.default_rng(11).uniform(0, 1, (lat.q,) + shape).astype(np.float32)
+        dec = SlabDecomposition()
+        x0, n = dec.local_range(shape[0])
+        slab = np.full((lat.q, n + 2, shape[1]), np.nan, np.float32)
+        slab[:, 1:-1] = f[:, x0 : x0 + n]
+        t = torch.from_numpy(slab)
+        HaloExchange(dec, lat).exchange(t.unsqueeze(-1))  # what DistributedStepper.exchange does for 2-D fields
+        got = t.numpy()
+        glob = ops.stream(lat, f)
+        local = np.empty((lat.q, n, shape[1]), np.float32)
+        for l in range(lat.q):
+            cx, cy = (int(v) for v in lat.c[:, l])
+            local[l] = np.roll(got[l, 1 - cx : 1 - cx + n], cy, axis=1)
+        assert np.array_equal(local, glob[:, x0 : x0 + n])
+        open(os.path.join(out_dir, f"ok{rank}"), "w").write("ok")
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,shape", [(2, (8, 6)), (3, (10, 5))])
+def test_halo_ring_gloo_2d(world, shape, tmp_path):
+    mp.spawn(_worker_2d, args=(world, _free_port(), shape, str(tmp_path)), nprocs=world, join=True)
+    assert all((tmp_path / f"ok{r}").exists() for r in range(world))
+
+
 def test_slab_partition():
     from xlb_b200.distribute import SlabDecomposition
 
@@ -75,6 +109,7 @@ def test_slab_partition():
                 assert a + n == b
     d = SlabDecomposition(0, 4)
     assert (d.left, d.right) == (3, 1)
+    assert d.local_range(19, rank=3) == (15, 4) and d.local_range(19, rank=0) == (0, 5)
     with pytest.raises(ValueError):
         SlabDecomposition(1, 8).local_range(8)
 

@@ -1,4 +1,5 @@
-"""N-rank x-slab run (NCCL halo ring, overlapped schedule) == single-GPU run, bitwise.  Needs >= 2 GPUs."""
+"""N-rank slab run (halo push fused into the edge launch over peer memory, CUDA-graph replay; NCCL schedule; 2-D and 3-D)
+== single-GPU run, bitwise.  Needs >= 2 GPUs."""
 
 import os
 import socket
@@ -26,4 +27,4 @@ def test_slab_run_equals_single_gpu(world):
            "--master-port", str(_free_port()), os.path.join(ROOT, "tests", "mgpu_worker.py")]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=ROOT)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
-    assert r.stdout.count("OK ") == 10, r.stdout
+    assert r.stdout.count("OK ") == 21, r.stdout

@@ -177,19 +177,26 @@ def test_error_paths():
     case = cases.cavity3d(8)
     st, _ = build_product(case)
     f_0, f_1, bc_mask, missing = st.prepare_fields()
+    # Operator.__call__ re-raises as a plain Exception like the reference (operator.py:128-133); the typed error is the cause
+    for bad in (
+        lambda: st(f_0, f_0, bc_mask, missing, 1.0, 0),  # same buffer
+        lambda: st(f_0.double(), f_1, bc_mask, missing, 1.0, 0),  # wrong store dtype
+        lambda: st(f_0.cpu(), f_1, bc_mask, missing, 1.0, 0),  # host tensor: no CPU path
+        lambda: st(f_0[:, ::2], f_1[:, ::2], bc_mask, missing, 1.0, 0),  # non-contiguous
+    ):
+        with pytest.raises(Exception) as info:
+            bad()
+        assert type(info.value) is Exception and isinstance(info.value.__cause__, ValueError)
     with pytest.raises(ValueError):
-        st(f_0, f_0, bc_mask, missing, 1.0, 0)  # same buffer
-    with pytest.raises(ValueError):
-        st(f_0.double(), f_1, bc_mask, missing, 1.0, 0)  # wrong store dtype
-    with pytest.raises(ValueError):
-        st(f_0.cpu(), f_1, bc_mask, missing, 1.0, 0)  # host tensor: no CPU path
-    with pytest.raises(ValueError):
-        st(f_0[:, ::2], f_1[:, ::2], bc_mask, missing, 1.0, 0)  # non-contiguous
+        st.launch_range(f_0, f_0, bc_mask, missing, 1.0, 0, 0, 8)  # the C-ABI layer itself keeps the typed errors
 
 
 @pytest.mark.parametrize("case,chunk", [(cases.sphere3d((48, 24, 24)), 7), (cases.cavity3d(0, shape=(21, 12, 16), omega=1.7), 4),
                                          (cases.periodic((16, 8, 8), lattice="D3Q27", collision="KBC"), 16),
-                                         (cases.cavity3d(16, policy="FP32FP16", omega=1.5), 5)], ids=lambda v: v["name"] if isinstance(v, dict) else str(v))
+                                         (cases.cavity3d(16, policy="FP32FP16", omega=1.5), 5),
+                                         # the wrapped stepper's collision parameters travel with it: body force, LES constant
+                                         (cases.cavity3d(16, omega=1.7, force=(1e-4, 2e-5, 0.0)), 6),
+                                         (cases.sphere3d((48, 24, 24), collision="SmagorinskyLESBGK", omega=1.9, force=(2e-5, 0.0, 1e-5)), 9)], ids=lambda v: v["name"] if isinstance(v, dict) else str(v))
 def test_host_streamed_step_equals_resident(case, chunk):
     """HostStreamedStepper (pinned host populations, x-chunk pipeline over three streams) == resident step, bitwise."""
     from xlb_b200.operator.stepper import HostStreamedStepper
@@ -249,7 +256,10 @@ def test_bulk_variant_rejects_unaligned_shapes():
     st, _ = build_product(case, backend_config={"kernel_variant": _lib.VARIANT_BULK})
     f_0, f_1, bc_mask, missing = st.prepare_fields()
     with pytest.raises(ValueError):
+        st.launch_range(f_0, f_1, bc_mask, missing, 1.0, 0, 0, 4)
+    with pytest.raises(Exception) as info:
         st(f_0, f_1, bc_mask, missing, 1.0, 0)
+    assert isinstance(info.value.__cause__, ValueError)
 
 
 def test_bulk_variant_many_steps_and_slab_ranges():
@@ -365,6 +375,37 @@ def test_bc_cell_list_follows_mask_updates():
     g_1 = torch.zeros_like(f_1)
     ref(f_0, g_1, bc_mask, missing, case["omega"], 0)
     assert torch.equal(f_1, g_1)
+
+
+def test_bc_cell_list_follows_remasking_through_the_c_abi():
+    """The maskers write bc_mask through raw pointers (invisible to torch's version counter): re-running a masker on the
+    same tensor must still invalidate the cached list."""
+    from xlb_b200.operator.boundary_masker import IndicesBoundaryMasker
+
+    case = cases.sphere3d((48, 24, 24))
+    st, bcs = build_product(case, backend_config={"bc_cell_list": True})
+    f_0, f_1, bc_mask, missing = st.prepare_fields()
+    n_before = st._cells[1].numel()
+    # tag one more inlet-kind cell in place with the inlet's id, through the masker
+    inlet = [bc for bc in bcs if int(bc.abi_kind) == _lib.BC_ZOUHE_VELOCITY][0]
+    inlet.indices = [[5], [7], [9]]
+    IndicesBoundaryMasker(velocity_set=st.velocity_set, precision_policy=st.precision_policy, compute_backend=st.compute_backend, grid=st.grid)(
+        [inlet], bc_mask, missing)
+    st(f_0, f_1, bc_mask, missing, case["omega"], 0)
+    n_after = st._cells[1].numel()
+    assert n_after > n_before
+    st.invalidate_bc_cells()
+    st(f_0, f_1, bc_mask, missing, case["omega"], 0)
+    assert st._cells[1].numel() == n_after
+
+
+def test_second_prepare_fields_fails_loudly():
+    """The maskers consume bc.indices (indices_boundary_masker.py:131): a second prepare_fields() with the same BC objects
+    raises like the reference instead of returning empty masks."""
+    st, _ = build_product(cases.cavity3d(8))
+    st.prepare_fields()
+    with pytest.raises(AttributeError):
+        st.prepare_fields()
 
 
 # ----------------------------------------------------------------------------- FP16 storage: packed half2 kernel

@@ -1,9 +1,12 @@
 """Ray-cast mesh masker: MeshMaskerRay (ray.py:43-77, mesh_boundary_masker.py:157-245).
 
-The reference has no JAX path and no tests for this operator, and its intersection routine lives in warp-lang (absent):
-PARITY UNPINNED -- the oracle (oracle/mesh_masker.py) restates the published watertight ray/triangle algorithm.  CPU
-tests check the oracle against geometry it must reproduce (analytic sphere shell, exact box faces); GPU tests compare the
-CUDA kernel with the oracle bit for bit (masks) / to the last bit (distance weights), and run a stepper on a mesh BC.
+The reference has no JAX path and no tests for this operator, and its intersection routine lives in warp-lang (absent), so
+the oracle (oracle/mesh_masker.py) restates the published watertight ray/triangle algorithm.  It is pinned here against
+geometry it must reproduce (analytic sphere shell, exact box faces, exact segment clipping of a convex mesh) and against a
+second, independent implementation (FP64 Moeller-Trumbore, oracle/mesh_moller.py) on non-convex meshes, thin plates,
+coincident faces and grazing rays; what remains unpinned is agreement with Warp's own BVH query, which cannot run here.
+GPU tests compare the CUDA kernel with the oracle bit for bit (masks) / to the last bit (distance weights) on all of
+these meshes, and run a stepper on a mesh BC.
 """
 
 import numpy as np
@@ -64,6 +67,77 @@ def test_oracle_out_of_bound_resolution():
             assert ms[l, 0, 4, 4]
 
 
+# ----------------------------------------------------------------------------- oracle vs a second implementation
+# the watertight FP32 restatement is pinned against an independent FP64 Moeller-Trumbore link test
+# (oracle/mesh_moller.py, which states its edge / vertex / interval conventions) on non-convex meshes, a plate thinner
+# than a cell, coincident faces, and rays that graze shared edges and vertices.
+def _grazing_box():
+    # corners at (k + 0.25) on all three axes: the face-diagonal rays from the cell centres pass exactly through the box's
+    # edges, the cube-diagonal rays exactly through its corners (at t = 0.75), and no cell centre lies on a face
+    return omm.box_mesh((4.25, 4.25, 4.25), (9.25, 9.25, 9.25))
+
+
+def _box_faces_on_cell_centres():
+    # faces on half-integer planes: axis rays from the cell centres (x + 0.5) run IN the faces' planes and along the box's edges
+    return omm.box_mesh((4.5, 3.5, 5.5), (9.5, 8.5, 10.5))
+
+
+from oracle import mesh_moller as omt  # noqa: E402
+
+PIN_MESHES = [
+    # name, lattice, shape, mesh factory, exact (True: coordinates are dyadic rationals, both implementations are exact -> no link may differ)
+    ("torus", "D3Q27", (26, 26, 14), lambda: omt.torus(7.3, 2.6, (12.7, 13.1, 6.6)), False),
+    ("l_bracket", "D3Q27", (16, 16, 12), lambda: omt.l_bracket((3.25, 4.25, 2.75)), True),
+    ("l_bracket_on_cell_centres", "D3Q19", (16, 16, 12), lambda: omt.l_bracket((3.5, 4.5, 2.5), arm=6.0, thick=3.0, height=5.0), True),
+    ("touching_boxes", "D3Q27", (20, 12, 12), lambda: omt.touching_boxes((3.25, 2.75, 3.25), (4.5, 5.0, 4.5)), True),
+    ("thin_plate", "D3Q27", (12, 14, 14), lambda: omt.thin_plate((5.6, 2.25, 2.75), 8.0, thickness=0.3), True),
+    ("thin_plate_between_centres", "D3Q19", (12, 14, 14), lambda: omt.thin_plate((5.625, 2.25, 2.75), 8.0, thickness=0.25), True),
+    ("grazing_box", "D3Q27", (15, 15, 15), _grazing_box, True),
+    ("box_faces_on_cell_centres", "D3Q27", (16, 14, 15), _box_faces_on_cell_centres, True),
+]
+
+
+@pytest.mark.parametrize("name,lattice,shape,mesh,exact", PIN_MESHES, ids=[m[0] for m in PIN_MESHES])
+def test_oracle_agrees_with_moller_trumbore(name, lattice, shape, mesh, exact):
+    lat = _lat(lattice)
+    verts = mesh()
+    bc, ms = _fields(lat.q, shape)
+    omm.mesh_masker_ray(lat, verts, 3, bc, ms)
+    links = omt.mesh_links(lat, verts, shape)
+    any_hit = np.zeros(shape, bool)
+    n_hits = n_skipped = 0
+    for l, (cells, hit, margin) in links.items():
+        got = ms[lat.opp_indices[l]][cells[:, 0], cells[:, 1], cells[:, 2]]
+        # exact meshes: every link is compared, grazing ones included (margin 0), except cell centres lying ON a face (margin -1)
+        safe = margin >= 0.0 if exact else margin > 1e-4
+        bad = np.flatnonzero((got != hit) & safe)
+        assert bad.size == 0, f"{name}, direction {l} {tuple(lat.c[:, l])}: {bad.size} links differ, first at cell {cells[bad[0]]} (watertight {got[bad[0]]}, Moeller-Trumbore {hit[bad[0]]}, margin {margin[bad[0]]:.2e})"
+        n_hits += int(hit.sum())
+        n_skipped += int((~safe).sum())
+        any_hit[cells[hit, 0], cells[hit, 1], cells[hit, 2]] = True
+    # "on_cell_centres": faces pass through cell centres on purpose; the links that start or end ON a face are outside the
+    # contract (see oracle/mesh_moller.py) and only the remaining ones are compared
+    degenerate = "on_cell_centres" in name
+    assert n_hits > 200 and (degenerate or n_skipped < 0.02 * sum(len(v[0]) for v in links.values()))
+    if exact and not degenerate:
+        assert np.array_equal(bc[0] == 3, any_hit)  # the tagged set is exactly the set of cells with a crossing link
+    # the mesh is strictly inside the domain: nothing outside the candidate box is touched
+    assert np.array_equal(bc[0] == 3, ms.any(axis=0))
+
+
+def test_thin_plate_is_seen_from_both_sides():
+    """A plate thinner than a cell between two cell centres: the link across it crosses the surface twice; both cells are
+    tagged and miss the direction towards each other (no leak through thin features)."""
+    lat = olat.D3Q19()
+    shape = (12, 14, 14)
+    bc, ms = _fields(19, shape)
+    omm.mesh_masker_ray(lat, omt.thin_plate((5.625, 2.25, 2.75), 8.0, thickness=0.25), 6, bc, ms)
+    lpx = [l for l in range(19) if tuple(lat.c[:, l]) == (1, 0, 0)][0]
+    lmx = lat.opp_indices[lpx]
+    assert bc[0, 5, 6, 6] == 6 and bc[0, 6, 6, 6] == 6 and bc[0, 4, 6, 6] == 0 and bc[0, 7, 6, 6] == 0
+    assert ms[lmx, 5, 6, 6] and ms[lpx, 6, 6, 6]  # (5,6,6) casts along +x and hits -> missing[opp(+x)]
+
+
 # ----------------------------------------------------------------------------- CUDA kernel vs oracle
 MESHES = [
     ("icosphere_q27", "D3Q27", (24, 20, 22), lambda: omm.icosphere(5.3, (11.2, 9.7, 10.4), 2)),
@@ -71,7 +145,7 @@ MESHES = [
     ("box_integer_planes", "D3Q27", (16, 14, 15), lambda: omm.box_mesh((4, 3, 5), (9, 8, 10))),
     ("box_half_planes", "D3Q19", (16, 14, 15), lambda: omm.box_mesh((4.5, 3.5, 5.5), (9.5, 8.5, 10.5))),
     ("box_touching_edge", "D3Q19", (10, 9, 8), lambda: omm.box_mesh((0.25, 2, 2), (3, 6, 6))),
-]
+] + [(m[0], m[1], m[2], m[3]) for m in PIN_MESHES]  # the meshes the oracle is pinned on: non-convex, thin, coincident faces, grazing rays
 
 
 def _lat(name):

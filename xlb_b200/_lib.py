@@ -10,7 +10,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("XLB_B200_LIB", os.path.join(_HERE, "_lib", "libxlb_b200.so"))
 
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 # enums of include/xlb_b200.h
 BGK, KBC, SMAGORINSKY_LES_BGK = 0, 1, 2
@@ -45,6 +45,14 @@ class XlbCollisionParams(Structure):
         ("bc_cells", c_void_p),
         ("n_bc_cells", c_int64),
     ]
+
+
+class XlbStepRange(Structure):
+    _fields_ = [("x_begin", c_int32), ("x_stride", c_int32), ("n_planes", c_int32), ("y_begin", c_int32), ("y_stride", c_int32), ("n_rows", c_int32)]
+
+
+class XlbHaloPush(Structure):
+    _fields_ = [("peer_f1", c_void_p * 2), ("src", c_int32 * 2), ("dst", c_int32 * 2)]
 
 
 class XlbBcEntry(Structure):
@@ -82,6 +90,13 @@ EXPORTS = {
     "xlb_launch_count": (c_longlong, []),
     "xlb_step": (c_int, [POINTER(XlbDomain), c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_double, c_int, c_int, c_int, c_int, c_void_p]),
     "xlb_step_ex": (c_int, [POINTER(XlbDomain), c_int, POINTER(XlbCollisionParams), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_double, c_int, c_int, c_int, c_int, c_void_p]),
+    "xlb_step_range": (c_int, [POINTER(XlbDomain), c_int, POINTER(XlbCollisionParams), POINTER(XlbStepRange), POINTER(XlbHaloPush), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_double, c_int, c_int, c_void_p]),
+    "xlb_halo_signal": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
+    "xlb_halo_wait": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
+    "xlb_ipc_export": (c_int, [c_void_p, c_void_p, POINTER(c_int64)]),
+    "xlb_ipc_import": (c_int, [c_void_p, c_int64, POINTER(c_void_p), POINTER(c_void_p)]),
+    "xlb_ipc_close": (c_int, [c_void_p]),
+    "xlb_copy_runs": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int, c_void_p]),
     "xlb_list_bc_cells": (c_int, [POINTER(XlbDomain), c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p]),
     "xlb_stream": (c_int, [POINTER(XlbDomain), c_int, c_void_p, c_void_p, c_void_p]),
     "xlb_macroscopic": (c_int, [POINTER(XlbDomain), c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),

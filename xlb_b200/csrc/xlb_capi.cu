@@ -88,14 +88,39 @@ int xlb_step(const XlbDomain* dom, int collision, const void* f0, void* f1, cons
 int xlb_step_ex(const XlbDomain* dom, int collision, const XlbCollisionParams* cp, const void* f0, void* f1, const uint8_t* bc_mask,
                 const uint8_t* missing_mask, const XlbBcEntry* bc_table, int n_bc, double omega, int timestep, int x_begin, int x_end,
                 int variant, void* stream) {
+    if (x_begin > x_end) return set_error(XLB_EINVAL, "xlb_step: bad x range");
+    XlbStepRange r;
+    r.x_begin = x_begin;
+    r.x_stride = 1;
+    r.n_planes = x_end - x_begin;
+    r.y_begin = 0;
+    r.y_stride = 1;
+    r.n_rows = 0;
+    return xlb_step_range(dom, collision, cp, &r, nullptr, f0, f1, bc_mask, missing_mask, bc_table, n_bc, omega, timestep, variant, stream);
+}
+
+int xlb_step_range(const XlbDomain* dom, int collision, const XlbCollisionParams* cp, const XlbStepRange* range, const XlbHaloPush* halo,
+                   const void* f0, void* f1, const uint8_t* bc_mask, const uint8_t* missing_mask, const XlbBcEntry* bc_table, int n_bc,
+                   double omega, int timestep, int variant, void* stream) {
     (void)timestep;  // carried for signature parity with nse_stepper.py:229; the JAX path never reads it
     if (int rc = check_domain(dom, "xlb_step")) return rc;
     if (!f0 || !f1) return set_error(XLB_EINVAL, "xlb_step: null population pointer");
     if (f0 == f1) return set_error(XLB_EINVAL, "xlb_step: f0 and f1 must be distinct buffers (pull scheme, double buffered)");
-    if (x_begin < 0 || x_end > dom->nx || x_begin > x_end) return set_error(XLB_EINVAL, "xlb_step: bad x range");
-    if (!dom->x_periodic && (x_begin < 1 || x_end > dom->nx - 1) && dom->d == 3)
+    XlbStepRange r;
+    if (range) {
+        r = *range;
+    } else {
+        r.x_begin = 0, r.x_stride = 1, r.n_planes = dom->nx;
+        r.y_begin = 0, r.y_stride = 1, r.n_rows = 0;
+    }
+    if (r.n_rows == 0) r.y_begin = 0, r.y_stride = 1, r.n_rows = dom->ny;
+    if (r.n_planes < 0 || r.n_rows < 0 || r.x_stride < 1 || r.y_stride < 1) return set_error(XLB_EINVAL, "xlb_step: bad plane / row range");
+    if (r.n_planes == 0 || r.n_rows == 0) return 0;
+    const int x_last = r.x_begin + (r.n_planes - 1) * r.x_stride, y_last = r.y_begin + (r.n_rows - 1) * r.y_stride;
+    if (r.x_begin < 0 || x_last >= dom->nx) return set_error(XLB_EINVAL, "xlb_step: bad x range");
+    if (r.y_begin < 0 || y_last >= dom->ny) return set_error(XLB_EINVAL, "xlb_step: bad y range");
+    if (!dom->x_periodic && (r.x_begin < 1 || x_last > dom->nx - 2) && dom->d == 3)
         return set_error(XLB_EINVAL, "xlb_step: non-periodic x needs ghost planes at x_begin-1 and x_end");
-    if (x_begin == x_end) return 0;
     StepParams p;
     std::memset(&p, 0, sizeof(p));
     p.f0 = f0;
@@ -108,8 +133,13 @@ int xlb_step_ex(const XlbDomain* dom, int collision, const XlbCollisionParams* c
     p.nx = dom->nx;
     p.ny = dom->ny;
     p.nz = dom->nz;
-    p.x_begin = x_begin;
-    p.x_end = x_end;
+    p.x_begin = r.x_begin;
+    p.x_end = x_last + 1;
+    p.x_stride = r.x_stride;
+    p.n_planes = r.n_planes;
+    p.y_begin = r.y_begin;
+    p.y_stride = r.y_stride;
+    p.n_rows = r.n_rows;
     p.x_periodic = dom->x_periodic;
     const long long ncell = (long long)dom->nx * dom->ny * dom->nz;
     p.qs = dom->q_stride ? dom->q_stride : ncell;
@@ -117,6 +147,21 @@ int xlb_step_ex(const XlbDomain* dom, int collision, const XlbCollisionParams* c
     p.omega = omega;
     p.bc_kind_mask = cp ? cp->bc_kind_mask : 0;
     p.halfway_fraction = cp ? (float)cp->halfway_fraction : 0.f;
+    if (halo) {
+        // slab axis: x planes for the 3-D lattices, rows (kernel y) for D2Q9
+        const int extent = dom->d == 3 ? dom->nx : dom->ny;
+        const long long unit = dom->d == 3 ? (long long)dom->ny * dom->nz : (long long)dom->nz;
+        for (int k = 0; k < 2; ++k) {
+            if (!halo->peer_f1[k]) continue;
+            if (halo->src[k] < 0 || halo->src[k] >= extent || halo->dst[k] < 0) return set_error(XLB_EINVAL, "xlb_step: bad XlbHaloPush plane");
+            if (halo->peer_f1[k] == f1 || halo->peer_f1[k] == f0) return set_error(XLB_EINVAL, "xlb_step: XlbHaloPush.peer_f1 must be the NEIGHBOUR's buffer");
+            p.peer[k] = halo->peer_f1[k];
+            p.peer_src[k] = halo->src[k];
+            p.peer_off[k] = (long long)halo->dst[k] * unit;
+        }
+        if (p.peer[0] && p.peer[1] && p.peer_src[0] == p.peer_src[1])
+            return set_error(XLB_EINVAL, "xlb_step: the slab must own at least two planes (first and last owned plane coincide)");
+    }
     if (cp && cp->bc_cells) {
         if (cp->n_bc_cells < 0 || cp->n_bc_cells >= (1ll << 37)) return set_error(XLB_EINVAL, "xlb_step: bad n_bc_cells");
         p.cells = reinterpret_cast<const long long*>(cp->bc_cells);
@@ -149,6 +194,121 @@ int xlb_step_ex(const XlbDomain* dom, int collision, const XlbCollisionParams* c
         XLB_CASES(27)
         default: return set_error(XLB_EUNSUPPORTED, "xlb_step: unsupported precision policy (precision_policy.py:57-97)");
     }
+}
+
+// ----------------------------------------------------------------------------- halo push ordering, peer mapping, batch copies
+namespace xlb {
+__global__ void halo_signal_kernel(unsigned long long* sent, unsigned long long* left_flag, unsigned long long* right_flag) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    const unsigned long long v = *sent + 1ull;
+    *sent = v;
+    // every store of the edge launch that preceded this kernel on the stream (the pushes into the neighbours' ghost planes
+    // included) happens-before this fence; the release stores then publish "push number v has landed"
+    __threadfence_system();
+    if (left_flag) asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(left_flag), "l"(v) : "memory");
+    if (right_flag) asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(right_flag), "l"(v) : "memory");
+}
+__global__ void halo_wait_kernel(unsigned long long* waited, const unsigned long long* from_left, const unsigned long long* from_right) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    const unsigned long long need = waited[0];
+    const unsigned long long* flags[2] = {from_left, from_right};
+    unsigned long long t0, t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (int k = 0; k < 2; ++k) {
+        if (!flags[k]) continue;
+        unsigned long long v;
+        do {
+            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(flags[k]) : "memory");
+            if (v < need) {
+                __nanosleep(64);
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                if (t1 - t0 > 30000000000ull) {  // 30 s without the neighbour's signal: it is gone.  Record it, never hang the GPU
+                    waited[1] = need;
+                    break;
+                }
+            }
+        } while (v < need);
+    }
+    waited[0] = need + 1ull;
+}
+}  // namespace xlb
+
+int xlb_halo_signal(uint64_t* sent, uint64_t* left_neighbours_flag, uint64_t* right_neighbours_flag, void* stream) {
+    if (!sent) return set_error(XLB_EINVAL, "xlb_halo_signal: null counter");
+    halo_signal_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<unsigned long long*>(sent),
+                                                                          reinterpret_cast<unsigned long long*>(left_neighbours_flag),
+                                                                          reinterpret_cast<unsigned long long*>(right_neighbours_flag));
+    return count_launch(cudaGetLastError());
+}
+
+int xlb_halo_wait(uint64_t* waited, const uint64_t* flag_from_left, const uint64_t* flag_from_right, void* stream) {
+    if (!waited) return set_error(XLB_EINVAL, "xlb_halo_wait: null counter");
+    halo_wait_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<unsigned long long*>(waited),
+                                                                        reinterpret_cast<const unsigned long long*>(flag_from_left),
+                                                                        reinterpret_cast<const unsigned long long*>(flag_from_right));
+    return count_launch(cudaGetLastError());
+}
+
+static int cuda_rc(cudaError_t e, const char* what) {
+    if (e == cudaSuccess) return 0;
+    std::snprintf(g_err, sizeof(g_err), "%s: CUDA error %d: %s", what, (int)e, cudaGetErrorString(e));
+    cudaGetLastError();  // clear the sticky-free error state
+    return (int)e;
+}
+
+int xlb_ipc_export(const void* dptr, void* handle, int64_t* offset) {
+    if (!dptr || !handle || !offset) return set_error(XLB_EINVAL, "xlb_ipc_export: null pointer");
+    // base of the allocation that contains dptr: cuMemGetAddressRange through the runtime's driver entry point (no libcuda link)
+    typedef int (*get_range_t)(unsigned long long*, size_t*, unsigned long long);
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    if (int rc = cuda_rc(cudaGetDriverEntryPoint("cuMemGetAddressRange", &fn, cudaEnableDefault, &qr), "xlb_ipc_export")) return rc;
+    if (!fn || qr != cudaDriverEntryPointSuccess) return set_error(XLB_EUNSUPPORTED, "xlb_ipc_export: cuMemGetAddressRange is not available");
+    unsigned long long base = 0;
+    size_t size = 0;
+    const int drc = reinterpret_cast<get_range_t>(fn)(&base, &size, (unsigned long long)reinterpret_cast<uintptr_t>(dptr));
+    if (drc != 0) return set_error(XLB_EINVAL, "xlb_ipc_export: not a device allocation");
+    cudaIpcMemHandle_t h;
+    if (int rc = cuda_rc(cudaIpcGetMemHandle(&h, reinterpret_cast<void*>(base)), "xlb_ipc_export")) return rc;
+    static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    std::memcpy(handle, &h, sizeof(h));
+    *offset = (int64_t)(reinterpret_cast<uintptr_t>(dptr) - base);
+    return 0;
+}
+
+int xlb_ipc_import(const void* handle, int64_t offset, void** dptr, void** base) {
+    if (!handle || !dptr || !base || offset < 0) return set_error(XLB_EINVAL, "xlb_ipc_import: bad argument");
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle, sizeof(h));
+    void* b = nullptr;
+    if (int rc = cuda_rc(cudaIpcOpenMemHandle(&b, h, cudaIpcMemLazyEnablePeerAccess), "xlb_ipc_import")) return rc;
+    *base = b;
+    *dptr = static_cast<char*>(b) + offset;
+    return 0;
+}
+
+int xlb_ipc_close(void* base) {
+    if (!base) return 0;
+    return cuda_rc(cudaIpcCloseMemHandle(base), "xlb_ipc_close");
+}
+
+int xlb_copy_runs(void* dst, int64_t dst_stride_bytes, const void* src, int64_t src_stride_bytes, int64_t run_bytes, int n_runs, void* stream) {
+    if (!dst || !src || run_bytes < 0 || n_runs < 0) return set_error(XLB_EINVAL, "xlb_copy_runs: bad argument");
+    if (run_bytes == 0 || n_runs == 0) return 0;
+    if (n_runs > 1 && (dst_stride_bytes < run_bytes || src_stride_bytes < run_bytes)) return set_error(XLB_EINVAL, "xlb_copy_runs: runs overlap");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int dev = 0, max_pitch = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&max_pitch, cudaDevAttrMaxPitch, dev);
+    if (n_runs == 1) return cuda_rc(cudaMemcpyAsync(dst, src, (size_t)run_bytes, cudaMemcpyDefault, st), "xlb_copy_runs");
+    if (dst_stride_bytes <= max_pitch && src_stride_bytes <= max_pitch)  // one 2-D copy: row = run, pitch = stride
+        return cuda_rc(cudaMemcpy2DAsync(dst, (size_t)dst_stride_bytes, src, (size_t)src_stride_bytes, (size_t)run_bytes, (size_t)n_runs, cudaMemcpyDefault, st),
+                       "xlb_copy_runs");
+    for (int r = 0; r < n_runs; ++r)  // strides beyond the 2-D copy's pitch limit (e.g. 1024^3 populations): run by run
+        if (int rc = cuda_rc(cudaMemcpyAsync(static_cast<char*>(dst) + r * dst_stride_bytes, static_cast<const char*>(src) + r * src_stride_bytes,
+                                             (size_t)run_bytes, cudaMemcpyDefault, st), "xlb_copy_runs"))
+            return rc;
+    return 0;
 }
 
 int xlb_stream(const XlbDomain* dom, int dtype, const void* f_in, void* f_out, void* stream) {

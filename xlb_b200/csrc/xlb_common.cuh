@@ -169,7 +169,9 @@ struct StepParams {
     const uint8_t* missing;
     const XlbBcEntry* bct;
     int nx, ny, nz;
-    int x_begin, x_end;
+    int x_begin, x_end;      // planes updated: x_begin + k * x_stride, k < n_planes (x_end = one past the last of them)
+    int x_stride, n_planes;
+    int y_begin, y_stride, n_rows;  // rows updated in each plane: y_begin + k * y_stride, k < n_rows (whole planes: 0, 1, ny)
     int x_periodic;
     int ntz;  // nz / V
     int ntz_shift;  // log2(ntz) when ntz is a power of two, else -1
@@ -182,7 +184,43 @@ struct StepParams {
     double force3[3];  // 3 * force_vector, kernel axes (exact_difference_force.py:72-75)
     const long long* cells;  // XlbCollisionParams.bc_cells: cells of listed BC kinds, updated by step_cells_kernel
     long long n_cells;
+    // halo push (XlbHaloPush): while updating slab-axis coordinate peer_src[k], the populations that leave the slab through
+    // that side (c = -1 for k = 0, +1 for k = 1) are ALSO stored into the neighbour's buffer peer[k] (peer-mapped memory,
+    // same q stride) at element offset peer_off[k] + (offset of the cell inside its plane / row)
+    void* peer[2];
+    long long peer_off[2];
+    int peer_src[2];
 };
+
+// slab axis of the multi-GPU decomposition in kernel axes: x for the 3-D lattices, y (= user x) for D2Q9, whose fields
+// run as nx = 1
+template <int Q>
+XLB_HD constexpr int slab_axis() { return Q == 9 ? 1 : 0; }
+
+// where a thread's outgoing populations go on the neighbour (nullptr / c = 0: nowhere)
+template <typename S>
+struct PeerDst {
+    S* base;  // neighbour's population 0 at this thread's cell(s); population l is at base + l * qs
+    int c;    // lattice component along the slab axis that crosses this side: -1 or +1
+};
+template <typename S, int Q>
+XLB_D PeerDst<S> peer_dst(const StepParams& p, int x, int y, long long offset_in_plane) {
+    PeerDst<S> d{nullptr, 0};
+    if (p.peer[0] == nullptr && p.peer[1] == nullptr) return d;
+    const int coord = slab_axis<Q>() == 0 ? x : y;
+    const long long inner = slab_axis<Q>() == 0 ? offset_in_plane : offset_in_plane - (long long)y * p.nz;
+    if (coord == p.peer_src[0] && p.peer[0] != nullptr) {
+        d.base = static_cast<S*>(p.peer[0]) + (p.peer_off[0] + inner);
+        d.c = -1;
+    } else if (coord == p.peer_src[1] && p.peer[1] != nullptr) {
+        d.base = static_cast<S*>(p.peer[1]) + (p.peer_off[1] + inner);
+        d.c = 1;
+    }
+    return d;
+}
+// compile-time component of direction (cx, cy) along the slab axis
+template <int Q>
+XLB_HD constexpr int slab_c(int cx, int cy) { return slab_axis<Q>() == 0 ? cx : cy; }
 
 // collision template codes: low bits = model (XLB_BGK / XLB_KBC / XLB_SMAGORINSKY_LES_BGK), bit 2 = exact-difference force
 #define XLB_COLL_FORCED 4

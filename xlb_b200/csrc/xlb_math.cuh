@@ -204,35 +204,10 @@ XLB_D float pick(const bool* flag, float a, float b) { return flag[0] ? a : b; }
 XLB_D double pick(const bool* flag, double a, double b) { return flag[0] ? a : b; }
 XLB_D F2 pick(const bool* flag, F2 a, F2 b) { return {make_float2(flag[0] ? a.v.x : b.v.x, flag[1] ? a.v.y : b.v.y)}; }
 
-// F4 = two independent F2 streams (four cells).  Same packed instructions, twice the instruction-level parallelism per
-// warp: the FP16-storage kernel runs at 10-12 warps per SM, where a single F2 dependency chain leaves the issue slots
-// two-thirds empty (profiles/r1t_ncu_details_f16_h2_v8.txt).
-struct F4 {
-    F2 a, b;
-};
-XLB_D F4 operator+(F4 x, F4 y) { return {x.a + y.a, x.b + y.b}; }
-XLB_D F4 operator-(F4 x) { return {-x.a, -x.b}; }
-XLB_D F4 operator-(F4 x, F4 y) { return {x.a - y.a, x.b - y.b}; }
-XLB_D F4 operator*(F4 x, F4 y) { return {x.a * y.a, x.b * y.b}; }
-XLB_D F4 fma_(F4 x, F4 y, F4 z) { return {fma_(x.a, y.a, z.a), fma_(x.b, y.b, z.b)}; }
-template <>
-struct Num<F4> {
-    using scalar = float;
-    static constexpr int lanes = 4;
-};
-template <>
-XLB_D F4 splat<F4>(float s) { return {splat<F2>(s), splat<F2>(s)}; }
-XLB_D F4 fast_div(F4 x, F4 y) { return {fast_div(x.a, y.a), fast_div(x.b, y.b)}; }
-XLB_D F4 sqrt_of(F4 x) { return {sqrt_of(x.a), sqrt_of(x.b)}; }
-XLB_D F4 rcp_of(F4 x) { return {rcp_of(x.a), rcp_of(x.b)}; }
-XLB_D F4 pick(const bool* flag, F4 x, F4 y) { return {pick(flag, x.a, y.a), pick(flag + 2, x.b, y.b)}; }
-
 // columns J .. J+lanes-1 of f[l] as one number, and back
 template <typename N, typename T, int Q, int V>
 XLB_D N col_get(const T (&f)[Q][V], int l, int J) {
-    if constexpr (Num<N>::lanes == 4) {
-        return N{F2{make_float2(f[l][J], f[l][J + 1])}, F2{make_float2(f[l][J + 2], f[l][J + 3])}};
-    } else if constexpr (Num<N>::lanes == 2) {
+    if constexpr (Num<N>::lanes == 2) {
         return N{make_float2(f[l][J], f[l][J + 1])};
     } else {
         return f[l][J];
@@ -240,12 +215,7 @@ XLB_D N col_get(const T (&f)[Q][V], int l, int J) {
 }
 template <typename N, typename T, int Q, int V>
 XLB_D void col_set(T (&f)[Q][V], int l, int J, N x) {
-    if constexpr (Num<N>::lanes == 4) {
-        f[l][J] = x.a.v.x;
-        f[l][J + 1] = x.a.v.y;
-        f[l][J + 2] = x.b.v.x;
-        f[l][J + 3] = x.b.v.y;
-    } else if constexpr (Num<N>::lanes == 2) {
+    if constexpr (Num<N>::lanes == 2) {
         f[l][J] = x.v.x;
         f[l][J + 1] = x.v.y;
     } else {
@@ -280,22 +250,13 @@ XLB_D uint32_t f2_to_h2(float a, float b) {
 }
 template <typename N, int Q, int W>
 XLB_D N col_get(const PackedH2<Q, W>& f, int l, int J) {
-    static_assert(Num<N>::lanes == 2 || Num<N>::lanes == 4, "packed fp16 storage is read one or two pairs at a time");
-    if constexpr (Num<N>::lanes == 4) {
-        return N{F2{h2_to_f2(f.w[l][J >> 1])}, F2{h2_to_f2(f.w[l][(J >> 1) + 1])}};
-    } else {
-        return N{h2_to_f2(f.w[l][J >> 1])};
-    }
+    static_assert(Num<N>::lanes == 2, "packed fp16 storage is read one pair at a time");
+    return N{h2_to_f2(f.w[l][J >> 1])};
 }
 template <typename N, int Q, int W>
 XLB_D void col_set(PackedH2<Q, W>& f, int l, int J, N x) {
-    static_assert(Num<N>::lanes == 2 || Num<N>::lanes == 4, "packed fp16 storage is written one or two pairs at a time");
-    if constexpr (Num<N>::lanes == 4) {
-        f.w[l][J >> 1] = f2_to_h2(x.a.v.x, x.a.v.y);
-        f.w[l][(J >> 1) + 1] = f2_to_h2(x.b.v.x, x.b.v.y);
-    } else {
-        f.w[l][J >> 1] = f2_to_h2(x.v.x, x.v.y);
-    }
+    static_assert(Num<N>::lanes == 2, "packed fp16 storage is written one pair at a time");
+    f.w[l][J >> 1] = f2_to_h2(x.v.x, x.v.y);
 }
 template <int Q, int W>
 XLB_D void col_swap(PackedH2<Q, W>& f, int l, int o, int J) {

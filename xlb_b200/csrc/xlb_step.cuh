@@ -119,8 +119,14 @@ XLB_D void cell_update_generic_impl(const StepParams& p, int x, int y, int z) {
             }
         });
     }
-#pragma unroll
-    for (int l = 0; l < Q; ++l) f1[l * p.qs + cell] = to_store<S, T>(f[l][0]);
+    const PeerDst<S> pd = peer_dst<S, Q>(p, x, y, (long long)y * p.nz + z);
+    static_for<Q>([&](auto lc) {
+        XLB_IDX(l, lc);
+        const S v = to_store<S, T>(f[l][0]);
+        f1[l * p.qs + cell] = v;
+        constexpr int ca = slab_c<Q>(Dir<Q, l>::cx, Dir<Q, l>::cy);
+        if (ca != 0 && pd.c == ca) pd.base[l * p.qs] = v;  // halo push: this population crosses into the neighbour's slab
+    });
 }
 
 template <typename T, typename S, int Q, int COLL>
@@ -131,11 +137,11 @@ __device__ __noinline__ void cell_update_generic(const StepParams& p, int x, int
 // every cell through the generic engine (variant XLB_VARIANT_GENERIC; cross-check + odd shapes)
 template <typename T, typename S, int Q, int COLL>
 __global__ void __launch_bounds__(128) step_generic_kernel(const __grid_constant__ StepParams p) {
-    const long long row = (long long)p.ny * p.nz;
+    const long long row = (long long)p.n_rows * p.nz;
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= row) return;
-    const int x = p.x_begin + blockIdx.y;
-    cell_update_generic_impl<T, S, Q, COLL>(p, x, (int)(i / p.nz), (int)(i % p.nz));
+    const int x = p.x_begin + blockIdx.y * p.x_stride;
+    cell_update_generic_impl<T, S, Q, COLL>(p, x, p.y_begin + (int)(i / p.nz) * p.y_stride, (int)(i % p.nz));
 }
 
 // the cells of the BC cell list (XlbCollisionParams.bc_cells) through the generic engine: consecutive threads take
@@ -157,7 +163,10 @@ __global__ void __launch_bounds__(128) step_cells_kernel(const __grid_constant__
         r = (int)(cell - x * plane);
     }
     const int y = r / p.nz;
-    if (x < p.x_begin || x >= p.x_end) return;
+    // only cells of the planes / rows this launch updates (a strided range lists e.g. the two edge planes of a slab)
+    const int dx = x - p.x_begin, dy = y - p.y_begin;
+    if (dx < 0 || dx % p.x_stride != 0 || dx / p.x_stride >= p.n_planes) return;
+    if (dy < 0 || dy % p.y_stride != 0 || dy / p.y_stride >= p.n_rows) return;
     cell_update_generic_impl<T, S, Q, COLL>(p, x, y, r - y * p.nz);
 }
 
@@ -180,15 +189,17 @@ XLB_D __half ld_if(const __half* ptr, bool pred, __half keep) {
 // HALF: the BC list holds a HalfwayBounceBackBC; its cells (obstacle surface AND interior -- every solid cell is tagged)
 // then take a vectorised in-register path instead of the per-cell generic engine.  It is a template flag because the
 // fast path of this kernel is register-critical: compiling the extra path into the BC-free / cavity instance costs 5-8 %.
-template <typename T, typename S, int Q, int COLL, int V, int BLOCK, int MINB, bool HAS_BC, bool HALF = false>
+// PUSH: the halo-push instance (XlbHaloPush) -- used for the edge-plane launch of a slab only; the instance that updates the
+// bulk of the lattice is compiled without it, because even three more live registers in the store loop cost it spills.
+template <typename T, typename S, int Q, int COLL, int V, int BLOCK, int MINB, bool HAS_BC, bool HALF = false, bool PUSH = false>
 __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_constant__ StepParams p) {
     const S* __restrict__ f0 = static_cast<const S*>(p.f0);
     S* __restrict__ f1 = static_cast<S*>(p.f1);
-    const int nvec = p.ny * p.ntz;  // vectors per x plane
+    const int nvec = p.n_rows * p.ntz;  // vectors per x plane
     int i = blockIdx.x * BLOCK + threadIdx.x;
     const bool active = i < nvec;
     if (!active) i = nvec - 1;  // keep the lane alive for the shuffles
-    const int x = p.x_begin + blockIdx.y;
+    const int x = p.x_begin + blockIdx.y * p.x_stride;
     int y, tz;
     if (p.ntz_shift >= 0) {
         y = i >> p.ntz_shift;
@@ -197,6 +208,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_c
         y = i / p.ntz;
         tz = i - y * p.ntz;
     }
+    y = p.y_begin + y * p.y_stride;
     const int z0 = tz * V;
     const int lane = threadIdx.x & 31;
     const long long plane = (long long)p.ny * p.nz;
@@ -329,16 +341,24 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_c
             collide_cols<T, T, Q, COLL, V, j>(f, ca, &k_full[j], HAS_BC && k_full[j]);
         });
     }
-    // ---- one aligned vector store per population
+    // ---- one aligned vector store per population (+ the halo push of the populations that leave the slab here)
     S* ql = f1 + cell;
-#pragma unroll
-    for (int l = 0; l < Q; ++l) {
+    PeerDst<S> pd{nullptr, 0};
+    if constexpr (PUSH) pd = peer_dst<S, Q>(p, x, y, (long long)y * p.nz + z0);
+    S* qp = pd.base;
+    static_for<Q>([&](auto lc) {
+        XLB_IDX(l, lc);
         Vec<S, V> o;
 #pragma unroll
         for (int j = 0; j < V; ++j) o.v[j] = to_store<S, T>(f[l][j]);
         st_vec<S, V>(ql, o);
         ql += p.qs;
-    }
+        if constexpr (PUSH) {
+            constexpr int ca = slab_c<Q>(Dir<Q, l>::cx, Dir<Q, l>::cy);
+            if (ca != 0 && pd.c == ca) st_vec<S, V>(qp, o);
+            qp += p.qs;
+        }
+    });
 }
 
 }  // namespace xlb

@@ -11,7 +11,8 @@
 //     the copy of population l (one row base + one 16-byte halo chunk where c_z != 0);
 //   * the +-1 z shift of the pull is a shared-memory index offset; every thread owns C cells NT apart, so all
 //     shared-memory reads are conflict-free 32-bit accesses and all global stores are fully coalesced.
-// Requirements (checked on the host, otherwise the vector kernel runs): nz % TZ == 0, 16-byte aligned rows.
+// Requirements (checked on the host, otherwise the vector kernel runs): nz % TZ == 0, 16-byte aligned rows, no halo push
+// (the edge-plane launch of a slab runs the vector kernel's PUSH instance).
 #pragma once
 #include "xlb_step.cuh"
 #include "xlb_step_h2.cuh"
@@ -85,8 +86,8 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
     const int tid = threadIdx.x;
     const int lane = tid & 31;
     const int nseg = p.nz / TZ;
-    const int tiles_per_plane = p.ny * nseg;
-    const int total = (p.x_end - p.x_begin) * tiles_per_plane;  // < 2^31, checked on the host
+    const int tiles_per_plane = p.n_rows * nseg;
+    const int total = p.n_planes * tiles_per_plane;  // < 2^31, checked on the host
     const long long plane = (long long)p.ny * p.nz;
 
     // lattice vector of the population this lane issues copies for
@@ -103,9 +104,10 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
     auto tile_coords = [&](int t, int& x, int& y, int& z0) {
         const int xr = t / tiles_per_plane;
         const int r = t - xr * tiles_per_plane;
-        y = r / nseg;
-        z0 = (r - y * nseg) * TZ;
-        x = p.x_begin + xr;
+        const int yr = r / nseg;
+        z0 = (r - yr * nseg) * TZ;
+        y = p.y_begin + yr * p.y_stride;
+        x = p.x_begin + xr * p.x_stride;
     };
     // one warp (all 32 lanes): fetch tile t into stage s
     auto issue = [&](int t, int s) {

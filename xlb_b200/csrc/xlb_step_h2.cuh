@@ -14,16 +14,16 @@
 #pragma once
 #include "xlb_step.cuh"
 
-// 1: BC-free groups of four cells collide as one F4 number (xlb_math.cuh: two independent packed streams, twice the ILP
-// per warp) on the packed storage.  Measured SLOWER on B200 (57.6 k vs 68.3 k MLUPS, profiles/sweep12_f16_quad_f4.log): the
-// doubled temporaries cost more than the extra ILP gains, so the kernel is not limited by per-warp dependency chains.
-#ifndef XLB_TUNE_H2_QUAD
-#define XLB_TUNE_H2_QUAD 0
-#endif
 // 1: always widen a pair to FP32 registers before the collision (one convert per element instead of one per read);
 // needs the register budget the V = 8 instance runs with (168-204 registers per thread), +2 % there
 #ifndef XLB_TUNE_H2_WIDEN
 #define XLB_TUNE_H2_WIDEN -1  // -1: widen where the register budget allows it (V = 8), profiles/sweep11_f16_*.log
+#endif
+
+// 1 (experiments only, results are WRONG): skip the collision -- same loads, z shifts and stores.  Separates "the access
+// pattern cannot go faster" from "the collision's registers / latency hold the loads back" (VERDICT r1 item 5).
+#ifndef XLB_TUNE_STREAM_ONLY
+#define XLB_TUNE_STREAM_ONLY 0
 #endif
 
 namespace xlb {
@@ -68,7 +68,7 @@ XLB_D void st_words(void* p, const uint32_t (&w)[W]) {
     }
 }
 
-template <int Q, int COLL, int V, int BLOCK, int MINB, bool HAS_BC, bool HALF>
+template <int Q, int COLL, int V, int BLOCK, int MINB, bool HAS_BC, bool HALF, bool PUSH = false>
 __global__ void __launch_bounds__(BLOCK, MINB) step_vector_h2_kernel(const __grid_constant__ StepParams p) {
     using T = float;
     using S = __half;
@@ -76,11 +76,11 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_h2_kernel(const __gri
     constexpr int W = V / 2;  // packed words per population
     const S* __restrict__ f0 = static_cast<const S*>(p.f0);
     S* __restrict__ f1 = static_cast<S*>(p.f1);
-    const int nvec = p.ny * p.ntz;
+    const int nvec = p.n_rows * p.ntz;
     int i = blockIdx.x * BLOCK + threadIdx.x;
     const bool active = i < nvec;
     if (!active) i = nvec - 1;
-    const int x = p.x_begin + blockIdx.y;
+    const int x = p.x_begin + blockIdx.y * p.x_stride;
     int y, tz;
     if (p.ntz_shift >= 0) {
         y = i >> p.ntz_shift;
@@ -89,6 +89,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_h2_kernel(const __gri
         y = i / p.ntz;
         tz = i - y * p.ntz;
     }
+    y = p.y_begin + y * p.y_stride;
     const int z0 = tz * V;
     const int lane = threadIdx.x & 31;
     const long long plane = (long long)p.ny * p.nz;
@@ -183,8 +184,6 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_h2_kernel(const __gri
     // (widened on access, narrowed once on the final set); pairs that hold an EquilibriumBC / half-way cell, and the
     // forced collisions (which read their own output), are widened to FP32 first so that every intermediate stays FP32.
     constexpr bool FORCED = (COLL & XLB_COLL_FORCED) != 0;
-    // QUAD: BC-free groups of four cells collide as one F4 (two independent packed streams: twice the ILP per warp)
-    constexpr bool QUAD = XLB_TUNE_H2_QUAD && (V % 4 == 0) && !FORCED && XLB_PACKED(COLL);
     auto do_pair = [&](auto jc, bool force_widen) {
         XLB_IDX(jp, jc);
         constexpr uint32_t PAIR = 3u << (2 * jp);
@@ -195,7 +194,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_h2_kernel(const __gri
             fw[0] = (m_full >> (2 * jp)) & 1u;
             fw[1] = (m_full >> (2 * jp + 1)) & 1u;
         }
-        constexpr bool WIDEN = XLB_TUNE_H2_WIDEN < 0 ? (V == 8 && !QUAD) : (XLB_TUNE_H2_WIDEN != 0);
+        constexpr bool WIDEN = XLB_TUNE_H2_WIDEN < 0 ? (V == 8) : (XLB_TUNE_H2_WIDEN != 0);
         if (FORCED || !XLB_PACKED(COLL) || pair_bc || WIDEN || force_widen) {
             T g[Q][2];
 #pragma unroll
@@ -248,33 +247,22 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_h2_kernel(const __gri
             collide_cols<F2, T, Q, COLL, V, 2 * jp>(pk, ca, fw, pair_full);
         }
     };
-    if constexpr (QUAD) {
-        static_for<V / 4>([&](auto qc) {
-            XLB_IDX(jq, qc);
-            constexpr uint32_t QUADM = 15u << (4 * jq);
-            if (HAS_BC && ((m_eq | m_half) & QUADM) != 0) {  // a streaming-step BC cell in the group: pair by pair
-                do_pair(std::integral_constant<int, 2 * jq>{}, false);
-                do_pair(std::integral_constant<int, 2 * jq + 1>{}, false);
-            } else {
-                const bool quad_full = HAS_BC && ((m_full & QUADM) != 0);
-                bool fw4[4] = {false, false, false, false};
-                if (quad_full) {
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) fw4[k] = (m_full >> (4 * jq + k)) & 1u;
-                }
-                collide_cols<F4, T, Q, COLL, V, 4 * jq>(pk, ca, fw4, quad_full);
-            }
-        });
-    } else {
-        static_for<W>([&](auto jc) { do_pair(jc, false); });
-    }
-    // ---- one aligned vector store per population
+    if constexpr (!XLB_TUNE_STREAM_ONLY) static_for<W>([&](auto jc) { do_pair(jc, false); });
+    // ---- one aligned vector store per population (+ the halo push of the populations that leave the slab here)
     S* ql = f1 + cell;
-#pragma unroll
-    for (int l = 0; l < Q; ++l) {
+    PeerDst<S> pd{nullptr, 0};
+    if constexpr (PUSH) pd = peer_dst<S, Q>(p, x, y, (long long)y * p.nz + z0);  // see step_vector_kernel
+    S* qp = pd.base;
+    static_for<Q>([&](auto lc) {
+        XLB_IDX(l, lc);
         st_words<W>(ql, raw[l]);
         ql += p.qs;
-    }
+        if constexpr (PUSH) {
+            constexpr int ca = slab_c<Q>(Dir<Q, l>::cx, Dir<Q, l>::cy);
+            if (ca != 0 && pd.c == ca) st_words<W>(qp, raw[l]);
+            qp += p.qs;
+        }
+    });
 }
 
 }  // namespace xlb

@@ -1,25 +1,18 @@
 // xlb_step_inst.cu -- one translation unit per (lattice, precision policy); compiled many times by
 // build.py with -DXLB_Q=<9|19|27> -DXLB_TC=<compute type> -DXLB_TS=<store type> -DXLB_TAG=<suffix>.
 // Exposes   int xlb_step_<tag>(const XlbDomain*, int collision, StepParams, int variant, cudaStream_t)
+#include <mutex>
+
 #include "xlb_host.cuh"
 #include "xlb_step.cuh"
 #include "xlb_step_bulk.cuh"
 #include "xlb_step_h2.cuh"
-#include "xlb_step_march.cuh"
 
 #ifndef XLB_Q
 #error "compile with -DXLB_Q -DXLB_TC -DXLB_TS -DXLB_TAG"
 #endif
 
 // tuning knobs (overridable from the command line for sweeps; see tools/sweep.py)
-// 1: the FP16-storage instances run step_march_h2_kernel (register double buffering along x, xlb_step_march.cuh) with
-// XLB_TUNE_XC planes per thread; experimental, see profiles/sweep13_f16_march.log
-#ifndef XLB_TUNE_MARCH
-#define XLB_TUNE_MARCH 0
-#endif
-#ifndef XLB_TUNE_XC
-#define XLB_TUNE_XC 16
-#endif
 // 1: FP32-compute / FP16-store instances run step_vector_h2_kernel (populations packed as half2 from load to store)
 #ifndef XLB_TUNE_H2
 #define XLB_TUNE_H2 1
@@ -39,7 +32,7 @@ constexpr int default_minb() { return sizeof(S) == 8 ? 4 : (Q == 27 ? 4 : (sizeo
 
 namespace xlb {
 
-template <typename T, typename S, int Q, int COLL, int V, bool HAS_BC, bool HALF = false>
+template <typename T, typename S, int Q, int COLL, int V, bool HAS_BC, bool HALF = false, bool PUSH = false>
 static int launch_vector(const StepParams& p0, cudaStream_t st) {
     constexpr bool USE_H2 = XLB_TUNE_H2 && std::is_same<S, __half>::value && std::is_same<T, float>::value && V >= 2;
 #ifdef XLB_TUNE_BLOCK_SET
@@ -52,20 +45,17 @@ static int launch_vector(const StepParams& p0, cudaStream_t st) {
     p.ntz_shift = -1;
     for (int b = 0; b < 31; ++b)
         if ((1 << b) == p.ntz) p.ntz_shift = b;
-    const long long nvec = (long long)p.ny * p.ntz;
-    dim3 grid((unsigned)((nvec + BLOCK - 1) / BLOCK), (unsigned)(p.x_end - p.x_begin), 1);
+    const long long nvec = (long long)p.n_rows * p.ntz;
+    dim3 grid((unsigned)((nvec + BLOCK - 1) / BLOCK), (unsigned)p.n_planes, 1);
 #ifdef XLB_TUNE_MINB
     constexpr int MINB = XLB_TUNE_MINB;
 #else
     constexpr int MINB = (V == 1) ? 4 : default_minb<S, Q, V>();
 #endif
-    if constexpr (USE_H2 && XLB_TUNE_MARCH) {
-        dim3 mgrid(grid.x, (unsigned)((p.x_end - p.x_begin + XLB_TUNE_XC - 1) / XLB_TUNE_XC), 1);
-        step_march_h2_kernel<Q, COLL, V, BLOCK, MINB, HAS_BC, HALF, XLB_TUNE_XC><<<mgrid, BLOCK, 0, st>>>(p);
-    } else if constexpr (USE_H2) {
-        step_vector_h2_kernel<Q, COLL, V, BLOCK, MINB, HAS_BC, HALF><<<grid, BLOCK, 0, st>>>(p);
+    if constexpr (USE_H2) {
+        step_vector_h2_kernel<Q, COLL, V, BLOCK, MINB, HAS_BC, HALF, PUSH><<<grid, BLOCK, 0, st>>>(p);
     } else {
-        step_vector_kernel<T, S, Q, COLL, V, BLOCK, MINB, HAS_BC, HALF><<<grid, BLOCK, 0, st>>>(p);
+        step_vector_kernel<T, S, Q, COLL, V, BLOCK, MINB, HAS_BC, HALF, PUSH><<<grid, BLOCK, 0, st>>>(p);
     }
     return count_launch(cudaGetLastError());
 }
@@ -100,19 +90,29 @@ static int launch_bulk(const StepParams& p, cudaStream_t st) {
     constexpr int BM0 = H2 ? XLB_TUNE_HBMINB : XLB_TUNE_BMINB;
     constexpr int BMINB = (BM0 * 128 / NT) > 0 ? (BM0 * 128 / NT) : 1;  // same register budget per thread for every NT
     auto kern = step_bulk_kernel<T, S, Q, COLL, C, NT, STAGES, BMINB, HAS_BC, HALF, H2>;
-    static int blocks_per_sm = 0, n_sm = 0;
+    // the shared-memory opt-in and the occupancy are per device: cached per device ordinal (one slot each, filled under a lock)
+    constexpr int MAX_DEV = 64;
+    static std::mutex mu;
+    static int cached_blocks[MAX_DEV] = {0}, cached_sms[MAX_DEV] = {0};
     const size_t smem = L::smem_bytes(STAGES);
-    if (blocks_per_sm == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return count_launch(e);
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kern, NT, smem);
-        if (e != cudaSuccess) return count_launch(e);
-        if (blocks_per_sm < 1) blocks_per_sm = 1;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    int blocks_per_sm = 0, n_sm = 0;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        const int slot = dev < MAX_DEV ? dev : MAX_DEV - 1;
+        if (cached_blocks[slot] == 0 || dev >= MAX_DEV) {
+            cudaDeviceGetAttribute(&cached_sms[slot], cudaDevAttrMultiProcessorCount, dev);
+            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e != cudaSuccess) return count_launch(e);
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&cached_blocks[slot], kern, NT, smem);
+            if (e != cudaSuccess) return count_launch(e);
+            if (cached_blocks[slot] < 1) cached_blocks[slot] = 1;
+        }
+        blocks_per_sm = cached_blocks[slot];
+        n_sm = cached_sms[slot];
     }
-    const long long total = (long long)(p.x_end - p.x_begin) * p.ny * (p.nz / TZ);
+    const long long total = (long long)p.n_planes * p.n_rows * (p.nz / TZ);
     if (total >= (1ll << 30)) return -1000;  // tile indices are 32-bit in the kernel
     long long grid = (long long)blocks_per_sm * n_sm;
     if (grid > total) grid = total;
@@ -124,7 +124,10 @@ template <typename T, typename S, int Q, int COLL, bool HAS_BC, bool HALF = fals
 static int try_bulk(const StepParams& p, cudaStream_t st) {
     constexpr int C = XLB_TUNE_C;
     const uintptr_t a0 = reinterpret_cast<uintptr_t>(p.f0), am = reinterpret_cast<uintptr_t>(p.bc_mask);
-    const bool aligned = (a0 % 16 == 0) && ((p.qs * sizeof(S)) % 16 == 0) && ((p.nz * sizeof(S)) % 16 == 0) && (!HAS_BC || am % 16 == 0);
+    bool aligned = (a0 % 16 == 0) && ((p.qs * sizeof(S)) % 16 == 0) && ((p.nz * sizeof(S)) % 16 == 0) && (!HAS_BC || am % 16 == 0);
+    // the half-way path of the packed-half2 consumer reads the missing bytes of a cell pair with one 16-bit load
+    if (HAS_BC && sizeof(S) == 2) aligned = aligned && reinterpret_cast<uintptr_t>(p.missing) % 2 == 0 && p.mqs % 2 == 0;
+    if (p.peer[0] || p.peer[1]) return -1000;  // halo push: the vector kernel's PUSH instance
     if (!aligned) return -1000;
     if constexpr (XLB_TUNE_H2 && std::is_same<S, __half>::value && std::is_same<T, float>::value) {
         if (p.nz % (128 * XLB_TUNE_HC) == 0) return launch_bulk<T, S, Q, COLL, XLB_TUNE_HC, 128, HAS_BC, HALF, true>(p, st);
@@ -144,8 +147,8 @@ static int try_bulk(const StepParams& p, cudaStream_t st) {
 
 template <typename T, typename S, int Q, int COLL>
 static int launch_generic(const StepParams& p, cudaStream_t st) {
-    const long long row = (long long)p.ny * p.nz;
-    dim3 grid((unsigned)((row + 127) / 128), (unsigned)(p.x_end - p.x_begin), 1);
+    const long long row = (long long)p.n_rows * p.nz;
+    dim3 grid((unsigned)((row + 127) / 128), (unsigned)p.n_planes, 1);
     step_generic_kernel<T, S, Q, COLL><<<grid, 128, 0, st>>>(p);
     return count_launch(cudaGetLastError());
 }
@@ -184,6 +187,19 @@ static int step_main(const StepParams& p, int variant, cudaStream_t st) {
         }
     };
     if (variant == XLB_VARIANT_GENERIC) return launch_generic<T, S, Q, COLL>(p, st);
+    const bool push = p.peer[0] != nullptr || p.peer[1] != nullptr;
+    if (push) {
+        // edge-plane launch of a slab with the halo push (XlbHaloPush): the vector kernel's PUSH instance where the shape allows
+        // the full vector width, else the generic kernel (every variant performs the same arithmetic, bit for bit)
+        const uintptr_t b0 = reinterpret_cast<uintptr_t>(p.f0), b1 = reinterpret_cast<uintptr_t>(p.f1);
+        bool ok = (p.nz % VMAX == 0) && (p.qs % VMAX == 0) && (b0 % (VMAX * sizeof(S)) == 0) && (b1 % (VMAX * sizeof(S)) == 0);
+        if (has_bc) ok = ok && reinterpret_cast<uintptr_t>(p.bc_mask) % VMAX == 0 && reinterpret_cast<uintptr_t>(p.missing) % VMAX == 0 && p.mqs % VMAX == 0;
+        for (int k = 0; k < 2; ++k)
+            if (p.peer[k]) ok = ok && reinterpret_cast<uintptr_t>(p.peer[k]) % (VMAX * sizeof(S)) == 0 && p.peer_off[k] % VMAX == 0;
+        if (!ok || variant == XLB_VARIANT_SCALAR) return launch_generic<T, S, Q, COLL>(p, st);
+        if (!has_bc) return launch_vector<T, S, Q, COLL, VMAX, false, false, true>(p, st);
+        return half ? launch_vector<T, S, Q, COLL, VMAX, true, true, true>(p, st) : launch_vector<T, S, Q, COLL, VMAX, true, false, true>(p, st);
+    }
     if (variant == XLB_VARIANT_BULK) {
         if constexpr (COLL == XLB_BGK || COLL == XLB_KBC) {
             const int rc = bulk();
@@ -194,8 +210,12 @@ static int step_main(const StepParams& p, int variant, cudaStream_t st) {
         }
     }
     const uintptr_t a0 = reinterpret_cast<uintptr_t>(p.f0), a1 = reinterpret_cast<uintptr_t>(p.f1);
+    // the vectorised paths move V bc_mask / missing_mask bytes and V populations per access: every base pointer and stride
+    // must be aligned to the vector
+    const uintptr_t am = reinterpret_cast<uintptr_t>(p.missing);
+    auto masks_ok = [&](int v) { return !has_bc || (reinterpret_cast<uintptr_t>(p.bc_mask) % v == 0 && am % v == 0 && p.mqs % v == 0); };
     const bool vec_ok = (p.nz % VMAX == 0) && (p.qs % VMAX == 0) && (a0 % (VMAX * sizeof(S)) == 0) && (a1 % (VMAX * sizeof(S)) == 0) &&
-                        (!has_bc || reinterpret_cast<uintptr_t>(p.bc_mask) % VMAX == 0);
+                        masks_ok(VMAX);
     if (variant == XLB_VARIANT_VECTOR && !vec_ok && !(VMAX == 8 && p.nz % 4 == 0)) return set_error(XLB_EALIGN, "xlb_step: vector variant needs nz, q_stride and base pointers aligned to the vector width");
     // AUTO: the bulk-staged pipeline where the B200 sweeps show it ahead of the vector kernel (D3Q27 KBC, compute-heavy)
     if constexpr (Q == 27 && COLL == XLB_KBC && sizeof(S) == 4) {
@@ -212,8 +232,7 @@ static int step_main(const StepParams& p, int variant, cudaStream_t st) {
     }
     if constexpr (VMAX == 8) {  // FP16 rows that are a multiple of 4 but not of 8 cells
         constexpr int V4 = 4;
-        const bool v4_ok = (p.nz % V4 == 0) && (p.qs % V4 == 0) && (a0 % (V4 * sizeof(S)) == 0) && (a1 % (V4 * sizeof(S)) == 0) &&
-                           (!has_bc || reinterpret_cast<uintptr_t>(p.bc_mask) % V4 == 0);
+        const bool v4_ok = (p.nz % V4 == 0) && (p.qs % V4 == 0) && (a0 % (V4 * sizeof(S)) == 0) && (a1 % (V4 * sizeof(S)) == 0) && masks_ok(V4);
         if (v4_ok && variant != XLB_VARIANT_SCALAR) {
             if (!has_bc) return launch_vector<T, S, Q, COLL, V4, false>(p, st);
             return half ? launch_vector<T, S, Q, COLL, V4, true, true>(p, st) : launch_vector<T, S, Q, COLL, V4, true, false>(p, st);

@@ -15,6 +15,18 @@ from ... import _lib
 from ...compute_backend import ComputeBackend
 from ..operator import Operator, byref, check, lib, stream_ptr
 
+_generation = [0]
+
+
+def mark_masks_written(*masks):
+    """The kernels write the masks through raw pointers, which torch cannot see: bump each tensor's version counter (an
+    in-place op on an empty view; no launch) and stamp a process-wide generation number, so that anything cached per mask
+    content -- the stepper's BC cell list -- notices the new content even at a recycled address."""
+    _generation[0] += 1
+    for m in masks:
+        m.view(-1)[:0].zero_()
+        m._xlb_generation = _generation[0]
+
 
 class IndicesBoundaryMasker(Operator):
     def __init__(self, velocity_set=None, precision_policy=None, compute_backend=None, grid=None):
@@ -66,4 +78,5 @@ class IndicesBoundaryMasker(Operator):
             del idx_dev
         check(lib().xlb_mask_missing(byref(dom), solid.data_ptr(), origin, gshape, missing_mask.data_ptr(), stream_ptr()), "IndicesBoundaryMasker")
         torch.cuda.current_stream().synchronize()  # index buffers above are freed on return
+        mark_masks_written(bc_mask, missing_mask)
         return bc_mask, missing_mask

@@ -17,6 +17,7 @@ import torch
 from ... import _lib
 from ...compute_backend import ComputeBackend
 from ..operator import Operator, byref, check, lib, stream_ptr
+from .indices_boundary_masker import mark_masks_written
 
 
 class MeshBoundaryMasker(Operator):
@@ -80,4 +81,5 @@ class MeshMaskerRay(MeshBoundaryMasker):
             weight = (keys & 0xFFFFFFFF).to(torch.int32).view(torch.float32)  # low word = bits of the distance weight
             distances[hit] = weight[hit].to(distances.dtype)  # ray.py:75-76
         torch.cuda.current_stream().synchronize()  # the triangle buffer is freed on return
+        mark_masks_written(bc_mask, missing_mask)
         return distances, bc_mask, missing_mask

@@ -32,39 +32,54 @@ class Operator:
         self._construct_cuda()
 
     # -- registration / dispatch (operator.py:74-133)
+    _signatures = {}  # registered function -> inspect.Signature (resolved once, not per call)
+    _bound = {}       # (class name, backend, n positional, keyword names) -> the implementation that bound last time
+
     @classmethod
     def register_backend(cls, backend_name):
         def decorator(func):
             owner = func.__qualname__.split(".")[0]
-            cls._backends[(owner, backend_name, str(inspect.signature(func)))] = func
+            sig = inspect.signature(func)
+            cls._backends[(owner, backend_name, str(sig))] = func
+            cls._signatures[func] = sig
+            cls._bound.clear()
             return func
 
         return decorator
 
     def __call__(self, *args, callback=None, **kwargs):
+        """Runs the first registered implementation of this class and backend whose signature binds the arguments
+        (operator.py:89-133).  As in the reference, whatever an implementation raises is re-raised as a plain
+        ``Exception`` that names the operator (operator.py:128-133); the original error is chained as ``__cause__``."""
         me = self.__class__.__name__
-        candidates = [(k, m) for k, m in self._backends.items() if k[0] == me and k[1] == self.compute_backend]
-        if not candidates:
-            have = [k for k in self._backends if k[0] == me]
-            raise NotImplementedError(f"No implementation found for operator {me} with backend {self.compute_backend}. Available implementations: {have}")
+        shape_key = (me, self.compute_backend, len(args), tuple(sorted(kwargs)))
+        method = self._bound.get(shape_key)
         key = error = trace = None
-        for key, method in candidates:
-            try:
-                inspect.signature(method).bind(self, *args, **kwargs)
-            except TypeError as exc:  # signature does not bind: try the next registered form
-                error, trace = exc, traceback.format_exc()
-                continue
+        if method is None:
+            candidates = [(k, m) for k, m in self._backends.items() if k[0] == me and k[1] == self.compute_backend]
+            if not candidates:
+                have = [k for k in self._backends if k[0] == me]
+                raise NotImplementedError(f"No implementation found for operator {me} with backend {self.compute_backend}. Available implementations: {have}")
+            for key, cand in candidates:
+                try:
+                    self._signatures[cand].bind(self, *args, **kwargs)
+                except TypeError as exc:  # signature does not bind: try the next registered form
+                    error, trace = exc, traceback.format_exc()
+                    continue
+                method = cand
+                self._bound[shape_key] = cand  # binding depends only on the argument count / keyword names
+                break
+        if method is not None:
             try:
                 result = method(self, *args, **kwargs)
-            except (NotImplementedError, ValueError):
-                raise  # unsupported combination / bad argument: keep the reference's exception types
             except Exception as exc:
                 error, trace = exc, traceback.format_exc()
-                continue
-            if callback and callable(callback):
-                callback(result if result is not None else (args, kwargs))
-            return result
-        raise Exception(f"Error captured for backend with key {key} for operator {me}: {error}\n {trace}")
+                key = (me, self.compute_backend, str(self._signatures[method]))
+            else:
+                if callback and callable(callback):
+                    callback(result if result is not None else (args, kwargs))
+                return result
+        raise Exception(f"Error captured for backend with key {key} for operator {me}: {error}\n {trace}") from error
 
     @property
     def supported_compute_backend(self):

@@ -10,10 +10,14 @@ travel.  This is the path ``bench.py`` times as ``e2e`` (host buffers in, host b
 run a lattice whose two population buffers exceed HBM (the reference's experimental out-of-core arrays,
 xlb/experimental/ooc, do the same with CuPy tiles).
 
-The per-cell arithmetic is the same ``xlb_step`` launch as the resident path (pull from ghost planes, x not periodic
-inside a chunk; the global periodic wrap is resolved when staging planes -1 and nx), so results are bit-identical to
-``stepper(f_0, f_1, ...)`` on device-resident fields.
+The per-cell arithmetic is the same ``xlb_step_ex`` launch as the resident path, with the wrapped stepper's collision
+parameters (LES constant, body force, BC kinds; pull from ghost planes, x not periodic inside a chunk; the global periodic
+wrap is resolved when staging planes -1 and nx), so results are bit-identical to ``stepper(f_0, f_1, ...)`` on
+device-resident fields.  Each chunk moves with ONE strided batch copy per direction (``xlb_copy_runs``: q runs of
+``planes * ny * nz`` elements), not q separate copies.
 """
+
+import ctypes
 
 import torch
 
@@ -53,27 +57,40 @@ class HostStreamedStepper:
                 b = nx if b - a < P else b - 1
             chunks.append((a, b))
             a = b
-        self._state = dict(shape=tuple(f_host.shape), P=P, bufs_in=bufs_in, bufs_out=bufs_out, streams=streams, table=table, n_bc=n_bc,
+        # the wrapped stepper's collision parameters (LES constant, force, BC kinds) without its BC cell list, whose
+        # indices refer to the resident block, not to a staged chunk
+        cp = _lib.XlbCollisionParams()
+        ctypes.memmove(ctypes.byref(cp), ctypes.byref(st._collision_params), ctypes.sizeof(cp))
+        cp.bc_cells, cp.n_bc_cells = None, 0
+        cp.halfway_fraction = 0.0
+        self._state = dict(shape=tuple(f_host.shape), P=P, cp=cp, bufs_in=bufs_in, bufs_out=bufs_out, streams=streams, table=table, n_bc=n_bc,
                            chunks=chunks,
                            ev_in=[torch.cuda.Event() for _ in range(2)], ev_done=[torch.cuda.Event() for _ in range(2)],
                            ev_out=[torch.cuda.Event() for _ in range(2)], ev_free_in=[torch.cuda.Event() for _ in range(2)])
         return self._state
 
-    def _stage(self, f_host, buf, a, b):
+    @staticmethod
+    def _copy_planes(dst, dst_plane, src, src_plane, n_planes, stream):
+        """planes [src_plane, src_plane + n) of every population of ``src`` -> planes [dst_plane, ...) of ``dst``: one batch copy."""
+        q = src.shape[0]
+        plane = src.shape[2] * src.shape[3]
+        esz = src.element_size()
+        rc = lib().xlb_copy_runs(
+            dst.data_ptr() + dst_plane * plane * esz, dst.stride(0) * esz, src.data_ptr() + src_plane * plane * esz, src.stride(0) * esz,
+            n_planes * plane * esz, q, _lib.c_void_p(stream.cuda_stream),
+        )
+        check(rc, "HostStreamedStepper")
+
+    def _stage(self, f_host, buf, a, b, stream):
         """planes a-1 .. b (periodic) of every population -> buf[:, 0 : b-a+2]"""
-        q, nx = f_host.shape[0], f_host.shape[1]
+        nx = f_host.shape[1]
         lo, hi = a - 1, b + 1
-        if lo >= 0 and hi <= nx:
-            for l in range(q):
-                buf[l, 0 : hi - lo].copy_(f_host[l, lo:hi], non_blocking=True)
-            return
-        for l in range(q):
-            s0, s1 = max(lo, 0), min(hi, nx)
-            buf[l, s0 - lo : s1 - lo].copy_(f_host[l, s0:s1], non_blocking=True)
-            if lo < 0:
-                buf[l, 0].copy_(f_host[l, nx - 1], non_blocking=True)
-            if hi > nx:
-                buf[l, hi - lo - 1].copy_(f_host[l, 0], non_blocking=True)
+        s0, s1 = max(lo, 0), min(hi, nx)
+        self._copy_planes(buf, s0 - lo, f_host, s0, s1 - s0, stream)
+        if lo < 0:
+            self._copy_planes(buf, 0, f_host, nx - 1, 1, stream)
+        if hi > nx:
+            self._copy_planes(buf, hi - lo - 1, f_host, 0, 1, stream)
 
     def __call__(self, f0_host, f1_host, bc_mask, missing_mask, omega, timestep):
         """``f0_host`` / ``f1_host``: pinned host tensors ``[q, nx, ny, nz]`` in the store dtype; masks on the device."""
@@ -101,7 +118,7 @@ class HostStreamedStepper:
             with torch.cuda.stream(h2d):
                 if k >= 2:
                     h2d.wait_event(s["ev_done"][i])
-                self._stage(f0_host, s["bufs_in"][i], a, b)
+                self._stage(f0_host, s["bufs_in"][i], a, b, h2d)
                 s["ev_in"][i].record(h2d)
             # ---- compute (output buffer i is free once chunk k-2 has been copied out)
             cur.wait_event(s["ev_in"][i])
@@ -117,8 +134,8 @@ class HostStreamedStepper:
             dom.mask_q_stride = nx * plane
             n_bc = s["n_bc"]
             off = (a - 1) * plane * esz_mask  # chunk-local plane 0 == global plane a-1 (never dereferenced for ghosts)
-            rc = lib().xlb_step(
-                byref(dom), st.collision.abi_model, s["bufs_in"][i].data_ptr(), s["bufs_out"][i].data_ptr(),
+            rc = lib().xlb_step_ex(
+                byref(dom), st.collision.abi_model, byref(s["cp"]), s["bufs_in"][i].data_ptr(), s["bufs_out"][i].data_ptr(),
                 (bc_mask.data_ptr() + off) if n_bc else None, (missing_mask.data_ptr() + off) if n_bc else None,
                 s["table"].data_ptr() if n_bc else None, n_bc, float(omega), int(timestep), 1, n + 1, st.kernel_variant,
                 _lib.c_void_p(cur.cuda_stream),
@@ -128,9 +145,7 @@ class HostStreamedStepper:
             # ---- stage out
             with torch.cuda.stream(d2h):
                 d2h.wait_event(s["ev_done"][i])
-                out = s["bufs_out"][i]
-                for l in range(q):
-                    f1_host[l, a:b].copy_(out[l, 1 : n + 1], non_blocking=True)
+                self._copy_planes(f1_host, a, s["bufs_out"][i], 1, n, d2h)
                 s["ev_out"][i].record(d2h)
         cur.wait_stream(d2h)
         cur.wait_stream(h2d)

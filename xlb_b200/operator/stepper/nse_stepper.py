@@ -111,6 +111,14 @@ class IncompressibleNavierStokesStepper(Stepper):
         return n / max(1, bc_mask.numel())
 
     def _process_boundary_conditions(self, boundary_conditions, bc_mask, missing_mask):
+        spent = [bc for bc in boundary_conditions if "indices" not in bc.__dict__ or "mesh_vertices" not in bc.__dict__]
+        if spent:
+            # the maskers consume bc.indices / bc.mesh_vertices (indices_boundary_masker.py:131, mesh_boundary_masker.py:203-204);
+            # the reference fails with an AttributeError on the second prepare_fields() -- fail as loudly, never mask nothing
+            raise AttributeError(
+                f"{spent[0].__class__.__name__} (id {spent[0].id}) has neither indices nor mesh_vertices left: prepare_fields() was already "
+                "called with these boundary-condition objects; build new BC objects (or clone the masks of the first call)"
+            )
         check_bc_overlaps(boundary_conditions, self.velocity_set.d, self.compute_backend)
         with_indices = [bc for bc in boundary_conditions if getattr(bc, "indices", None) is not None]
         if with_indices:
@@ -162,7 +170,8 @@ class IncompressibleNavierStokesStepper(Stepper):
         key = (tuple(f_0.shape), f_0.dtype, tuple(bc.id for bc in self.boundary_conditions))
         if self._plan is None or self._plan[0] != key:
             halo = getattr(self.grid, "halo", 0)
-            dom = self._domain(f_0, x_periodic=0 if halo else 1)
+            # a 3-D slab has ghost planes instead of the periodic wrap in x; a D2Q9 slab runs as nx = 1 with ghost ROWS
+            dom = self._domain(f_0, x_periodic=0 if (halo and self.velocity_set.d == 3) else 1)
             table, n_bc = self.build_bc_table(tuple(f_0.shape[1:]))
             x_begin, x_end = (halo, dom.nx - halo) if self.velocity_set.d == 3 else (0, dom.nx)
             self._plan = (key, dom, table, n_bc, x_begin, x_end)
@@ -178,7 +187,7 @@ class IncompressibleNavierStokesStepper(Stepper):
         outflow, do-nothing) plus its per-plane offsets, cached per ``bc_mask`` content.  ``xlb_step_ex`` then updates
         those cells with one dense launch over the list instead of diverging inside the fused kernel.  The reference
         specialises its kernel per BC list at construction (nse_stepper.py:351-380); this is the analogous setup step."""
-        key = (bc_mask.data_ptr(), bc_mask._version, tuple(bc_mask.shape))
+        key = (bc_mask.data_ptr(), bc_mask._version, getattr(bc_mask, "_xlb_generation", None), tuple(bc_mask.shape))
         if self._cells is not None and self._cells[0] == key:
             return self._cells
         self._cells = (key, None, None)
@@ -202,11 +211,23 @@ class IncompressibleNavierStokesStepper(Stepper):
         self._cells = (key, cells, offsets)
         return self._cells
 
+    def invalidate_bc_cells(self):
+        """Forget the cached BC cell list.  Needed only after ``bc_mask`` was rewritten behind torch's back (a raw-pointer
+        write from foreign code); torch in-place ops and this package's maskers are noticed automatically."""
+        self._cells = None
+
     # ------------------------------------------------------------------ the step
     def launch_range(self, f_0, f_1, bc_mask, missing_mask, omega, timestep, x_begin, x_end):
         """One ``xlb_step`` launch that updates planes ``[x_begin, x_end)`` of ``f_1`` (local plane indices, ghost
-        planes included in the numbering).  The multi-GPU schedule (xlb_b200/distribute) issues the two edge
-        planes and the interior as separate launches of this method."""
+        planes included in the numbering)."""
+        rng = _lib.XlbStepRange(int(x_begin), 1, int(x_end) - int(x_begin), 0, 1, 0)
+        self.launch(f_0, f_1, bc_mask, missing_mask, omega, timestep, rng)
+
+    def launch(self, f_0, f_1, bc_mask, missing_mask, omega, timestep, rng=None, halo=None):
+        """One ``xlb_step_range`` launch: the planes / rows of ``rng`` (an ``XlbStepRange``; ``None`` = the stepper's whole
+        block), optionally with the halo push ``halo`` (an ``XlbHaloPush``) of the outgoing edge populations into the ring
+        neighbours' buffers.  The multi-GPU schedule (xlb_b200/distribute) issues the two edge planes of a slab as ONE
+        strided launch with the push, and the interior as a second launch."""
         q = self.velocity_set.q
         if f_0.dtype != self.store_dtype or f_1.dtype != self.store_dtype:
             raise ValueError(f"populations must be stored as {self.store_dtype} under policy {self.precision_policy.name}")
@@ -214,27 +235,38 @@ class IncompressibleNavierStokesStepper(Stepper):
         self._check_field(f_1, "f_1", q)
         if f_0.shape != f_1.shape:
             raise ValueError("f_0 and f_1 must have the same shape")
-        _, dom, table, n_bc, _, _ = self._get_plan(f_0)
+        _, dom, table, n_bc, x_begin, x_end = self._get_plan(f_0)
+        if rng is None:
+            rng = self._whole_range(dom, x_begin, x_end)
         if n_bc:
             self._check_field(bc_mask, "bc_mask", 1)
             self._check_field(missing_mask, "missing_mask", q)
         cp = self._collision_params
         cp.bc_cells, cp.n_bc_cells = None, 0
-        if n_bc:
+        if n_bc and rng.n_planes > 0:
             _, cells, offsets = self._bc_cell_list(f_0, bc_mask)
             if cells is not None:
-                lo, hi = offsets[int(x_begin)], offsets[int(x_end)]
+                # the list slice that covers the launch's planes; the kernel skips entries of planes / rows in between
+                x_last = rng.x_begin + (rng.n_planes - 1) * rng.x_stride
+                lo, hi = offsets[int(rng.x_begin)], offsets[int(x_last) + 1]
                 if hi > lo:
                     cp.bc_cells, cp.n_bc_cells = cells.data_ptr() + 8 * lo, hi - lo
-        rc = lib().xlb_step_ex(
-            byref(dom), self.collision.abi_model, byref(cp) if cp is not None else None, f_0.data_ptr(), f_1.data_ptr(),
+        rc = lib().xlb_step_range(
+            byref(dom), self.collision.abi_model, byref(cp), byref(rng), byref(halo) if halo is not None else None, f_0.data_ptr(), f_1.data_ptr(),
             bc_mask.data_ptr() if n_bc else None, missing_mask.data_ptr() if n_bc else None, table.data_ptr() if n_bc else None, n_bc,
-            float(omega), int(timestep), int(x_begin), int(x_end), self.kernel_variant, stream_ptr(),
+            float(omega), int(timestep), self.kernel_variant, stream_ptr(),
         )
         check(rc, "IncompressibleNavierStokesStepper")
 
+    def _whole_range(self, dom, x_begin, x_end):
+        """The owned cells of this block: all of it, or -- on a slab grid -- everything but the ghost planes (3-D) /
+        ghost rows (D2Q9, whose fields run as nx = 1 with the user's x axis on the kernel's y axis)."""
+        halo = getattr(self.grid, "halo", 0)
+        if self.velocity_set.d == 2 and halo:
+            return _lib.XlbStepRange(0, 1, 1, halo, 1, int(dom.ny) - 2 * halo)
+        return _lib.XlbStepRange(int(x_begin), 1, int(x_end) - int(x_begin), 0, 1, 0)
+
     @Operator.register_backend(ComputeBackend.CUDA)
     def cuda_implementation(self, f_0, f_1, bc_mask, missing_mask, omega, timestep):
-        _, _, _, _, x_begin, x_end = self._get_plan(f_0)
-        self.launch_range(f_0, f_1, bc_mask, missing_mask, omega, timestep, x_begin, x_end)
+        self.launch(f_0, f_1, bc_mask, missing_mask, omega, timestep)
         return f_0, f_1
