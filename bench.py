@@ -152,7 +152,7 @@ def build_case(workload, slab=None, shape=None, variant=0, radius=None, backend_
     if slab is not None:
         grid = slab.make_grid(shape)
     else:
-        grid = xlb.grid.grid_factory(shape, compute_backend=ComputeBackend.CUDA)
+        grid = xlb.grid.grid_factory(shape, compute_backend=ComputeBackend.CUDA, backend_config={"slab": False})  # one whole block, also under torchrun
     nx, ny, nz = shape
     box = grid.bounding_box_indices()
     box_ne = grid.bounding_box_indices(remove_edges=True)

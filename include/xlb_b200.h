@@ -56,7 +56,9 @@ typedef struct XlbBcEntry {
     int32_t kind;         /* XLB_BC_* */
     int32_t pv_dtype;     /* element type of pv (XLB_F16/F32/F64) */
     int32_t normal[3];    /* ExtrapolationOutflowBC.normal, kernel axes (bc_extrapolation_outflow.py:78-92) */
-    int32_t reserved;
+    int32_t pv_mode;      /* velocity types: 0 = pv holds the velocity VECTOR (d components, the JAX convention, bc_zouhe.py:119-120);
+                             1 = pv holds ONE scalar per cell, the inflow speed along the inward normal, u = -value * normal (the
+                             Warp convention of a per-index profile, bc_zouhe.py:332-337, helper_functions_bc.py:417-473) */
     int64_t pv_stride[4]; /* strides (elements) of pv over (component, x, y, z); 0 = broadcast */
     const void* pv;       /* Zou-He prescribed values, device pointer (bc_zouhe.py:119-120, 178-215) */
     double table[27];     /* EQUILIBRIUM: feq_l (bc_equilibrium.py:74-76); HALFWAY: 6 w_l c_l.u_wall (bc_halfway_bounce_back.py:123-128) */

@@ -78,11 +78,19 @@ def test_one_step_parity_sphere_384x128x128():
 
 
 def _auto_equals_generic(workload, shape=None, steps=2, seed=3, backend_config=None):
+    from xlb_b200.operator.boundary_condition.boundary_condition_registry import boundary_condition_registry
+
+    boundary_condition_registry.next_id = 1
     auto, vs, pol, shape, omega = bench.build_case(workload, shape=shape, variant=_lib.VARIANT_AUTO, backend_config=backend_config)
     f_0, f_1, bc_mask, missing = auto.prepare_fields()
     del f_0
     f_0 = _device_random_state(vs, shape, f_1.dtype, seed=seed)
+    # the generic stepper runs on the masks of the first one (no second 2.7 GB missing_mask at 512^3): its BC objects must
+    # get the same ids, or its table would not know the ids stored in bc_mask and every wall would be updated as fluid
+    boundary_condition_registry.next_id = 1
     gen, _, _, _, _ = bench.build_case(workload, shape=shape, variant=_lib.VARIANT_GENERIC)
+    assert [b.id for b in gen.boundary_conditions] == [b.id for b in auto.boundary_conditions]
+    assert int(bc_mask.max()) == max(b.id for b in auto.boundary_conditions)
     g_1 = torch.empty_like(f_1)
     n0 = _lib.launch_count()
     for t in range(steps):

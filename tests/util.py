@@ -42,7 +42,7 @@ def build_product(case, backend_config=None, decomposition=None):
     if decomposition is not None:
         grid = decomposition.make_grid(case["shape"])
     else:
-        grid = grid_factory(case["shape"], compute_backend=ComputeBackend.CUDA)
+        grid = grid_factory(case["shape"], compute_backend=ComputeBackend.CUDA, backend_config={"slab": False})  # the whole block, also under torchrun
     bcs = []
     for spec in case["bcs"]:
         kind = spec["kind"]

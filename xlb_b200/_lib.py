@@ -60,7 +60,7 @@ class XlbBcEntry(Structure):
         ("kind", c_int32),
         ("pv_dtype", c_int32),
         ("normal", c_int32 * 3),
-        ("reserved", c_int32),
+        ("pv_mode", c_int32),
         ("pv_stride", c_int64 * 4),
         ("pv", c_void_p),
         ("table", c_double * 27),
@@ -73,7 +73,7 @@ BC_ENTRY_DTYPE = np.dtype(
         ("kind", np.int32),
         ("pv_dtype", np.int32),
         ("normal", np.int32, (3,)),
-        ("reserved", np.int32),
+        ("pv_mode", np.int32),
         ("pv_stride", np.int64, (4,)),
         ("pv", np.uint64),
         ("table", np.float64, (27,)),

@@ -566,4 +566,5 @@ int xlb_mask_mesh_ray(const XlbDomain* dom, const float* triangles, int64_t n_tr
     return count_launch(cudaGetLastError());
 }
 
+
 }  // extern "C"

@@ -635,10 +635,19 @@ XLB_D void zouhe_apply(T (&f)[Q][1], uint32_t miss, const XlbBcEntry& e, bool ve
     const long long pvo = (long long)x * e.pv_stride[1] + (long long)y * e.pv_stride[2] + (long long)z * e.pv_stride[3];
     if (velocity_type) {
         T un = T(0);
+        if (e.pv_mode == 1) {  // per-index profile of the Warp convention: one inflow speed per cell, u = -value * normal (:332-337)
+            const T speed = ld_any<T>(e.pv, e.pv_dtype, pvo);
 #pragma unroll
-        for (int a = A0; a < 3; ++a) {
-            vel[a] = ld_any<T>(e.pv, e.pv_dtype, pvo + (a - A0) * e.pv_stride[0]);
-            un += static_cast<T>(nrm[a]) * vel[a];
+            for (int a = A0; a < 3; ++a) {
+                vel[a] = -speed * static_cast<T>(nrm[a]);
+                un += static_cast<T>(nrm[a]) * vel[a];
+            }
+        } else {
+#pragma unroll
+            for (int a = A0; a < 3; ++a) {
+                vel[a] = ld_any<T>(e.pv, e.pv_dtype, pvo + (a - A0) * e.pv_stride[0]);
+                un += static_cast<T>(nrm[a]) * vel[a];
+            }
         }
         rho = fsum / (T(1.0) + un);  // :256-266
     } else {

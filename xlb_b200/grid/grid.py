@@ -7,12 +7,28 @@ from ..compute_backend import ComputeBackend, require_cuda_backend
 
 
 def grid_factory(shape, compute_backend=None, velocity_set=None, backend_config=None):
-    """Same call as the reference; only ``ComputeBackend.CUDA`` exists here."""
+    """Same call as the reference; only ``ComputeBackend.CUDA`` exists here.
+
+    The reference's JAX grid shards every field over all visible devices without being asked (jax_grid.py:22-36), and its
+    distributed example relies on that (examples/cfd/lid_driven_cavity_2d_distributed.py:22-27 calls the plain
+    ``grid_factory``).  The equivalent here, one process per GPU: when ``torch.distributed`` is initialised with more than
+    one rank, the grid returned is this rank's slab of ``shape`` (``SlabDecomposition.make_grid``).  ``backend_config={"slab":
+    False}`` asks for the whole block on this rank regardless."""
     compute_backend = compute_backend or DefaultConfig.default_backend
     require_cuda_backend(compute_backend)
     from .cuda_grid import CudaGrid
 
-    return CudaGrid(shape, backend_config=backend_config)
+    cfg = dict(backend_config or {})
+    slab = cfg.pop("slab", "auto")
+    if slab == "auto":
+        import torch.distributed as dist
+
+        slab = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+    if slab:
+        from ..distribute import SlabDecomposition
+
+        return SlabDecomposition().make_grid(shape, backend_config=cfg)
+    return CudaGrid(shape, backend_config=cfg)
 
 
 class Grid:

@@ -1,11 +1,21 @@
 """Zou-He velocity / pressure boundary condition (xlb/operator/boundary_condition/bc_zouhe.py:48-304).
 
-Prescribed data follow the JAX convention of the reference: ``prescribed_value`` (a velocity vector with
-one non-zero normal component, or a scalar density for ``"pressure"``) or a ``profile`` callable returning
-the full array, e.g. ``(d, ny, nz)`` for an x-face inlet (examples/cfd/flow_past_sphere_3d.py:58-81).  The
-array is kept in a side buffer on the device and addressed with broadcast strides -- nothing is encoded
-in ``f_1`` (that encoding is an artefact of the Warp backend, helper_functions_bc.py:371-562).
+Prescribed data: ``prescribed_value`` (a velocity vector with one non-zero normal component, or a scalar density for
+``"pressure"``) or a ``profile`` callable.  Both profile conventions of the reference are accepted, told apart by the
+callable's arity:
+
+* ``profile()`` -> the full array, e.g. ``(d, ny, nz)`` for an x-face inlet (the JAX convention,
+  examples/cfd/flow_past_sphere_3d.py:62-79, bc_zouhe.py:119-120);
+* ``profile(index)`` -> one value per boundary cell, the inflow speed along the inward normal (velocity) or the density
+  (pressure), ``index`` being the cell's integer coordinates (the Warp convention: a ``wp.func`` over ``wp.vec3i``,
+  flow_past_sphere_3d.py:89-102, bc_zouhe.py:332-337).  It is evaluated once, at construction, over the BC's index list
+  -- vectorised (``index[a]`` are NumPy arrays) where the function's body allows it, cell by cell otherwise.
+
+Either way the values live in a side buffer on the device and are addressed with broadcast strides -- nothing is
+encoded in ``f_1`` (that encoding is an artefact of the Warp backend, helper_functions_bc.py:371-562).
 """
+
+import inspect
 
 import numpy as np
 import torch
@@ -43,6 +53,13 @@ class ZouHeBC(BoundaryCondition):
             self.profile = lambda: np.array(prescribed_value, dtype=sdt).reshape(-1, 1)  # bc_zouhe.py:156-157
         if self.profile is None:
             raise ValueError("ZouHeBC needs either prescribed_value or profile")
+        self._pv_device = None
+        self._pv_box = None  # per-index profile: (lower corner of the index set's bounding box, dense value box)
+        fn = getattr(self.profile, "func", self.profile)  # a warp.Function keeps the Python function in .func
+        if len(inspect.signature(fn).parameters) >= 1:
+            self.prescribed_values = None
+            self._evaluate_index_profile(fn, indices)
+            return
         values = self.profile()  # evaluated eagerly like the JAX path (bc_zouhe.py:119-120)
         if isinstance(values, torch.Tensor):
             values = values.detach().cpu().numpy()
@@ -50,7 +67,30 @@ class ZouHeBC(BoundaryCondition):
         if values.dtype not in (np.float16, np.float32, np.float64):
             values = values.astype(self.precision_policy.store_precision.np_dtype)
         self.prescribed_values = values
-        self._pv_device = None
+
+    def _evaluate_index_profile(self, fn, indices):
+        """``profile(index) -> value`` over the BC's own cells, stored as a dense box around the index set."""
+        if indices is None:
+            raise NotImplementedError("a per-index profile needs the boundary condition's indices (mesh-based BCs: pass an array profile)")
+        idx = np.asarray(indices.detach().cpu() if isinstance(indices, torch.Tensor) else indices, dtype=np.int64).reshape(self.velocity_set.d, -1)
+        if idx.shape[1] == 0:
+            raise ValueError("a per-index profile needs a non-empty index list")
+        sdt = self.precision_policy.store_precision.np_dtype
+        if sdt == np.float16:
+            sdt = np.float32
+        full = tuple(idx) + ((np.zeros_like(idx[0]),) if idx.shape[0] == 2 else ())  # the reference always passes a vec3i
+        try:
+            values = np.asarray(fn(full), dtype=np.float64).reshape(-1)  # vectorised: index[a] are arrays
+            if values.size == 1:
+                values = np.full(idx.shape[1], float(values[0]))
+            if values.size != idx.shape[1]:
+                raise ValueError("profile did not broadcast over the index arrays")
+        except Exception:  # the body only works on scalars (e.g. real warp builtins): cell by cell
+            values = np.array([float(np.asarray(fn(tuple(int(v) for v in col))).reshape(-1)[0]) for col in np.stack(full, axis=1)])
+        lo = idx.min(axis=1)
+        box = np.zeros(tuple(idx.max(axis=1) - lo + 1), dtype=sdt)
+        box[tuple(idx - lo[:, None])] = values.astype(sdt)
+        self._pv_box = (lo, box)
 
     def _broadcast_shape(self, field_shape):
         """Shape rule of ``_broadcast_prescribed_values`` (bc_zouhe.py:178-215): singleton axes are inserted
@@ -74,6 +114,22 @@ class ZouHeBC(BoundaryCondition):
         super().bc_table_row(row, field_shape)
         if field_shape is None:
             raise ValueError("ZouHeBC needs the field shape to lay out its prescribed values")
+        if self._pv_box is not None:
+            # one value per cell (XlbBcEntry.pv_mode = 1), addressed by the kernel's local cell coordinates: axes along which the
+            # index set is one cell thick are broadcast, the others are shifted by the box corner minus the block's origin
+            lo, box = self._pv_box
+            if self._pv_device is None:
+                self._pv_device = torch.from_numpy(np.ascontiguousarray(box)).to(current_device())
+            pv = self._pv_device
+            origin = getattr(self, "_block_origin", None) or (0,) * self.velocity_set.d
+            strides = [0 if n == 1 else s for n, s in zip(box.shape, pv.stride())]
+            shift = sum(s * (int(origin[a]) - int(lo[a])) for a, s in enumerate(strides))
+            row["pv"] = pv.data_ptr() + shift * pv.element_size()
+            row["pv_dtype"] = abi_code_of(pv.dtype)
+            row["pv_mode"] = 1
+            row["pv_stride"][0] = 0
+            row["pv_stride"][1:] = kernel_axes(strides, self.velocity_set.d)
+            return
         shp = self._broadcast_shape(field_shape)
         if self._pv_device is None or tuple(self._pv_device.shape) != shp:
             self._pv_device = torch.from_numpy(np.ascontiguousarray(self.prescribed_values.reshape(shp))).to(current_device())

@@ -19,6 +19,7 @@ device-resident fields.  Each chunk moves with ONE strided batch copy per direct
 
 import ctypes
 
+import numpy as np
 import torch
 
 from ... import _lib
@@ -45,8 +46,9 @@ class HostStreamedStepper:
         streams = dict(h2d=torch.cuda.Stream(), d2h=torch.cuda.Stream())
         table, n_bc = st.build_bc_table((nx, ny, nz))
         for bc in st.boundary_conditions:  # prescribed-value arrays are addressed with chunk-local x
-            pv = getattr(bc, "_pv_device", None)
-            if pv is not None and pv.dim() >= 2 and pv.shape[1] != 1:
+            row = np.zeros(1, dtype=_lib.BC_ENTRY_DTYPE)
+            bc.bc_table_row(row[0], (nx, ny, nz))
+            if int(row["pv"][0]) != 0 and int(row["pv_stride"][0][1]) != 0:
                 raise NotImplementedError("HostStreamedStepper: prescribed profiles must be constant along x")
         # chunk list: [a, b) with the last chunk at least 2 planes thick (extrapolation outflow reads x-2)
         chunks = []

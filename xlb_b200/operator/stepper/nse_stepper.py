@@ -161,6 +161,8 @@ class IncompressibleNavierStokesStepper(Stepper):
         for bc in self.boundary_conditions:
             if not (1 <= bc.id <= 253):
                 raise ValueError(f"boundary-condition id {bc.id} does not fit bc_mask (1..253)")
+            # global coordinates of this block's cell 0 (slab grids carry ghost planes in front of their first owned plane)
+            bc._block_origin = (getattr(self.grid, "x_offset", 0) - getattr(self.grid, "halo", 0),) + (0,) * (self.velocity_set.d - 1)
             bc.bc_table_row(table[bc.id], field_shape)
             n_bc = max(n_bc, bc.id + 1)
         dev = torch.from_numpy(table.view(np.uint8).copy()).to(current_device())

@@ -37,6 +37,18 @@ class Precision(Enum):
         }[self]
 
     @property
+    def wp_dtype(self):
+        """Scalar constructor scripts use inside Warp-style per-index profiles (``wp_dtype(index[1])``,
+        examples/cfd/flow_past_sphere_3d.py:84-100).  This package evaluates such profiles on the host with NumPy, so the
+        NumPy scalar type is returned (it converts scalars and whole index arrays alike)."""
+        return self.np_dtype
+
+    @property
+    def jax_dtype(self):
+        """NumPy dtype standing in for the reference's ``jnp`` dtype accessor (precision_policy.py:39-54)."""
+        return self.np_dtype
+
+    @property
     def abi_code(self):
         return {Precision.FP64: XLB_F64, Precision.FP32: XLB_F32, Precision.FP16: XLB_F16, Precision.UINT8: XLB_U8, Precision.BOOL: XLB_U8}[self]
 
