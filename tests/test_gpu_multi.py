@@ -28,3 +28,16 @@ def test_slab_run_equals_single_gpu(world):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=ROOT)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert r.stdout.count("OK ") == 21, r.stdout
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_reference_distributed_example_runs_unchanged(world):
+    """examples/cfd/lid_driven_cavity_2d_distributed.py (the reference's only shipped use of distribute) on N ranks with only
+    the backend switched == the same cavity on one GPU, bitwise (tests/mgpu_example_worker.py)."""
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs, have {torch.cuda.device_count()}")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
+           "--master-port", str(_free_port()), os.path.join(ROOT, "tests", "mgpu_example_worker.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.stdout.count("OK lid_driven_cavity_2d_distributed.py") == 1, r.stdout

@@ -56,7 +56,9 @@ class ZouHeBC(BoundaryCondition):
         self._pv_device = None
         self._pv_box = None  # per-index profile: (lower corner of the index set's bounding box, dense value box)
         fn = getattr(self.profile, "func", self.profile)  # a warp.Function keeps the Python function in .func
-        if len(inspect.signature(fn).parameters) >= 1:
+        required = [a for a in inspect.signature(fn).parameters.values()
+                    if a.default is inspect.Parameter.empty and a.kind in (a.POSITIONAL_ONLY, a.POSITIONAL_OR_KEYWORD)]
+        if required:  # profile(index): the Warp convention; a callable without required arguments is the JAX convention
             self.prescribed_values = None
             self._evaluate_index_profile(fn, indices)
             return
