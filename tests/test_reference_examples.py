@@ -162,7 +162,10 @@ def test_lid_driven_cavity_2d_runs_unchanged(reference_environment):
     case = cases.cavity2d(n, omega=omega, u_lid=u_lid)
     ost, _ = cases.build_oracle(case)
     f0, f1, bc_o, mm_o = ost.prepare_fields()
-    assert np.array_equal(to_np(sim.bc_mask), bc_o) and np.array_equal(to_np(sim.missing_mask), mm_o)
+    # the script CONSTRUCTS the lid first (id 1) and the walls second (id 2) but LISTS them [walls, lid]; the oracle case numbers
+    # them in list order.  Same masks up to that relabelling (the write order, which decides overlaps, is the list order in both).
+    relabel = np.array([0, 2, 1], dtype=np.uint8)
+    assert np.array_equal(to_np(sim.bc_mask), relabel[bc_o]) and np.array_equal(to_np(sim.missing_mask), mm_o)
     ref, _ = ost.run(f0.astype(ost.sdt), f1, bc_o, mm_o, omega, steps)
     assert rel_err(to_np(sim.f_0), ref) <= 1e-5
 
@@ -187,7 +190,9 @@ def test_flow_past_sphere_3d_runs_unchanged(reference_environment):
     case = cases.sphere3d(shape, lattice="D3Q19", collision="BGK", omega=1.6, u_max=0.04, inlet="regularized_velocity", profile=True)
     ost, _ = cases.build_oracle(case)
     f0, f1, bc_o, mm_o = ost.prepare_fields()
-    assert np.array_equal(to_np(ns["bc_mask"]), bc_o) and np.array_equal(to_np(ns["missing_mask"]), mm_o)
+    # constructed: inlet (1), walls (2), outlet (3), sphere (4); listed [walls, inlet, outlet, sphere] like the oracle case
+    relabel = np.array([0, 2, 1, 3, 4], dtype=np.uint8)
+    assert np.array_equal(to_np(ns["bc_mask"]), relabel[bc_o]) and np.array_equal(to_np(ns["missing_mask"]), mm_o)
     ref, _ = ost.run(f0.astype(ost.sdt), f1, bc_o, mm_o, 1.6, steps)
     assert rel_err(to_np(ns["f_0"]), ref) <= 1e-5
 
