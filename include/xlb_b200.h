@@ -210,6 +210,23 @@ int xlb_mask_tag(const XlbDomain* dom, const int32_t* indices, int64_t n, const 
 int xlb_mask_missing(const XlbDomain* dom, const uint8_t* solid, const int32_t origin[3], const int32_t global_shape[3],
                      uint8_t* missing_mask, void* stream);
 
+/* Allocation-free variant of the indices masker (xlb_mask_tag + xlb_mask_missing above).  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving
+ * loops, harnesses that forbid allocation).  The two passes of the masker communicate through a per-cell ``solid`` scratch array
+ * that the caller of xlb_mask_tag / xlb_mask_missing has to allocate; here that scratch is a file-scope
+ * ``static __device__ __align__(256)`` array of XLB_MASK_STATIC_MAX_CELLS bytes inside the library (every GPU that loads the
+ * library holds these 16 MiB until the process exits).  The caller still passes the inputs (index list) and the outputs
+ * (bc_mask, missing_mask); the call itself allocates nothing -- no cudaMalloc / cudaFree, no allocating library routine.
+ *   begin  != 0 : clear the scratch first (it keeps the previous call's contents otherwise) -- pass it with the first BC of a list;
+ *   n > 0       : tag this BC exactly like xlb_mask_tag (same arguments), marking solid cells in the static scratch;
+ *   finish != 0 : then run the xlb_mask_missing pass from the scratch into missing_mask -- pass it with the last BC of a list.
+ * Blocks of more than XLB_MASK_STATIC_MAX_CELLS cells (nx*ny*nz) are rejected with XLB_EINVAL and a message.  All calls on a
+ * device share the ONE array: calls that overlap on the GPU (different streams, or concurrent graph branches) race; serialise
+ * them.  The array's address is resolved with cudaGetSymbolAddress once per device, with that device current. */
+#define XLB_MASK_STATIC_MAX_CELLS (16 * 1024 * 1024)
+int xlb_mask_indices_static(const XlbDomain* dom, const int32_t* indices, int64_t n, const int32_t origin[3], const int32_t global_shape[3],
+                            int id, int mark_solid, int pad, int begin, int finish, uint8_t* bc_mask, uint8_t* missing_mask, void* stream);
+
 /* MeshMaskerRay (boundary_masker/ray.py:43-77) + resolve_out_of_bound_kernel (mesh_boundary_masker.py:157-179): voxelises a triangle
  * soup (``triangles`` = float32 [n_triangles][3 vertices][3 coords], lattice units, GLOBAL kernel-axis coordinates, device
  * pointer).  Every cell of the local block from whose centre a lattice ray of length |c_l| hits the surface gets

@@ -12,6 +12,8 @@ LIB_PATH = os.environ.get("XLB_B200_LIB", os.path.join(_HERE, "_lib", "libxlb_b2
 
 ABI_VERSION = 4
 
+MASK_STATIC_MAX_CELLS = 16 * 1024 * 1024  # XLB_MASK_STATIC_MAX_CELLS
+
 # enums of include/xlb_b200.h
 BGK, KBC, SMAGORINSKY_LES_BGK = 0, 1, 2
 BC_NONE, BC_FULLWAY, BC_EQUILIBRIUM, BC_HALFWAY, BC_DONOTHING, BC_ZOUHE_VELOCITY, BC_ZOUHE_PRESSURE, BC_EXTRAPOLATION = range(8)
@@ -108,6 +110,7 @@ EXPORTS = {
     "xlb_momentum_transfer": (c_int, [POINTER(XlbDomain), c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "xlb_mask_tag": (c_int, [POINTER(XlbDomain), c_void_p, c_int64, POINTER(c_int32), POINTER(c_int32), c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "xlb_mask_missing": (c_int, [POINTER(XlbDomain), c_void_p, POINTER(c_int32), POINTER(c_int32), c_void_p, c_void_p]),
+    "xlb_mask_indices_static": (c_int, [POINTER(XlbDomain), c_void_p, c_int64, POINTER(c_int32), POINTER(c_int32), c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "xlb_mask_mesh_ray": (c_int, [POINTER(XlbDomain), c_void_p, c_int64, POINTER(c_int32), POINTER(c_int32), c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
 }
 

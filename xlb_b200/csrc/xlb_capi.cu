@@ -2,6 +2,7 @@
 #include <atomic>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 
 #include "xlb_host.cuh"
 #include "xlb_mesh.cuh"
@@ -566,5 +567,85 @@ int xlb_mask_mesh_ray(const XlbDomain* dom, const float* triangles, int64_t n_tr
     return count_launch(cudaGetLastError());
 }
 
+
+// ----------------------------------------------------------------------------- allocation-free indices masker
+// The per-cell ``solid`` scratch of the two masker passes, inside the library (see include/xlb_b200.h).  In HOST code the
+// name g_mask_solid_scratch is only a stand-in for the symbol: the device address is asked for with cudaGetSymbolAddress,
+// once per device with that device current, and that pointer is what the kernels get.
+}  // extern "C"
+static __device__ __align__(256) uint8_t g_mask_solid_scratch[XLB_MASK_STATIC_MAX_CELLS];
+
+static int mask_scratch_address(uint8_t** out) {
+    constexpr int MAX_DEV = 64;
+    static std::mutex mu;
+    static uint8_t* cached[MAX_DEV] = {nullptr};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return count_launch(e);
+    if (dev < 0 || dev >= MAX_DEV) return set_error(XLB_EUNSUPPORTED, "xlb_mask_indices_static: device ordinal beyond 63");
+    std::lock_guard<std::mutex> lock(mu);
+    if (cached[dev] == nullptr) {
+        void* ptr = nullptr;
+        e = cudaGetSymbolAddress(&ptr, g_mask_solid_scratch);  // the current device's instance of the array
+        if (e != cudaSuccess || ptr == nullptr) {
+            std::snprintf(g_err, sizeof(g_err), "xlb_mask_indices_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+            cudaGetLastError();
+            return e != cudaSuccess ? (int)e : XLB_EINVAL;
+        }
+        cached[dev] = static_cast<uint8_t*>(ptr);
+    }
+    *out = cached[dev];
+    return 0;
+}
+extern "C" {
+
+int xlb_mask_indices_static(const XlbDomain* dom, const int32_t* indices, int64_t n, const int32_t origin[3], const int32_t global_shape[3],
+                            int id, int mark_solid, int pad, int begin, int finish, uint8_t* bc_mask, uint8_t* missing_mask, void* stream) {
+    if (int rc = check_domain(dom, "xlb_mask_indices_static")) return rc;
+    const long long ncell = (long long)dom->nx * dom->ny * dom->nz;
+    if (ncell > (long long)XLB_MASK_STATIC_MAX_CELLS) {
+        std::snprintf(g_err, sizeof(g_err), "xlb_mask_indices_static: block of %lld cells exceeds the static scratch of %d cells (XLB_MASK_STATIC_MAX_CELLS); "
+                      "use xlb_mask_tag / xlb_mask_missing with a caller-allocated solid array", ncell, (int)XLB_MASK_STATIC_MAX_CELLS);
+        return XLB_EINVAL;
+    }
+    if (n < 0 || (n > 0 && !indices)) return set_error(XLB_EINVAL, "xlb_mask_indices_static: null indices");
+    if (n > 0 && !bc_mask && id >= 0) return set_error(XLB_EINVAL, "xlb_mask_indices_static: null bc_mask");
+    if (id > 255) return set_error(XLB_EINVAL, "xlb_mask_indices_static: id must fit a uint8");
+    if (finish && !missing_mask) return set_error(XLB_EINVAL, "xlb_mask_indices_static: finish needs missing_mask");
+    uint8_t* scratch = nullptr;
+    if (int rc = mask_scratch_address(&scratch)) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (begin) {  // the array keeps the last call's contents: everything the missing pass reads must start at zero
+        cudaError_t e = cudaMemsetAsync(scratch, 0, (size_t)ncell, st);
+        if (e != cudaSuccess) return count_launch(e);
+    }
+    if (n > 0) {
+        MaskParams p = make_mask(dom, origin, global_shape);
+        p.idx = indices;
+        p.n = n;
+        p.id = id;
+        p.mark_solid = mark_solid;
+        p.pad = pad;
+        p.bc_mask = bc_mask;
+        p.solid = scratch;
+        const long long total = pad ? n * dom->q : n;
+        const unsigned nb = blocks_for(total, 256);
+        if (dom->q == 9) mask_tag_kernel<9><<<nb, 256, 0, st>>>(p);
+        else if (dom->q == 19) mask_tag_kernel<19><<<nb, 256, 0, st>>>(p);
+        else mask_tag_kernel<27><<<nb, 256, 0, st>>>(p);
+        if (int rc = count_launch(cudaGetLastError())) return rc;
+    }
+    if (finish) {
+        MaskParams p = make_mask(dom, origin, global_shape);
+        p.solid_in = scratch;
+        p.missing = missing_mask;
+        const unsigned nb = blocks_for(ncell, 256);
+        if (dom->q == 9) mask_missing_kernel<9><<<nb, 256, 0, st>>>(p);
+        else if (dom->q == 19) mask_missing_kernel<19><<<nb, 256, 0, st>>>(p);
+        else mask_missing_kernel<27><<<nb, 256, 0, st>>>(p);
+        if (int rc = count_launch(cudaGetLastError())) return rc;
+    }
+    return 0;
+}
 
 }  // extern "C"
