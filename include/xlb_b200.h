@@ -102,13 +102,15 @@ typedef struct XlbStepRange {
  * While the step kernel updates slab-axis coordinate src[k] (the first owned plane for k = 0, the last owned plane for k = 1;
  * planes of a 3-D block, rows of a D2Q9 block) it stores the populations that cross that side of the slab (c = -1 for k = 0,
  * c = +1 for k = 1 along the slab axis: velocity_set.left_indices / right_indices) ALSO into the ring neighbour's f1 buffer --
- * a device pointer of another GPU mapped into this process (xlb_ipc_import), same layout and q_stride as f1 -- at its ghost
+ * a device pointer of another GPU mapped into this process (xlb_ipc_import), same plane layout as f1, its own q stride -- at its ghost
  * plane / row dst[k].  Compute and transfer are one kernel: the NVLink stores are posted while the rest of the slab is being
  * updated; no pack buffer, no collective call.  Ordering between ranks is the caller's (xlb_halo_signal / xlb_halo_wait). */
 typedef struct XlbHaloPush {
     void* peer_f1[2];   /* [0] left neighbour's f1, [1] right neighbour's f1; NULL = no push on that side */
     int32_t src[2];     /* my plane (row) whose outgoing populations are pushed: first owned, last owned */
     int32_t dst[2];     /* the neighbour's ghost plane (row) that receives them: its right ghost, its left ghost */
+    int64_t peer_q_stride[2]; /* elements between populations in THAT neighbour's buffer (slabs of unequal thickness have unequal
+                                 strides); 0 = the same as dom->q_stride */
 } XlbHaloPush;
 
 const char* xlb_last_error(void);

@@ -84,7 +84,8 @@ def main():
     grid = grid_factory((n, n), compute_backend=ComputeBackend.CUDA, backend_config={"slab": False})
     box, box_ne = grid.bounding_box_indices(), grid.bounding_box_indices(remove_edges=True)
     walls = np.unique(np.array([box["bottom"][i] + box["left"][i] + box["right"][i] for i in range(2)]), axis=-1).tolist()
-    bcs = [HalfwayBounceBackBC(indices=walls), EquilibriumBC(rho=1.0, u=(u_lid, 0.0), indices=box_ne["top"])]
+    bc_top = EquilibriumBC(rho=1.0, u=(u_lid, 0.0), indices=box_ne["top"])  # constructed first (id 1), listed second: as in the script (:52-56)
+    bcs = [HalfwayBounceBackBC(indices=walls), bc_top]
     st = IncompressibleNavierStokesStepper(grid=grid, boundary_conditions=bcs, collision_type="BGK")
     f_0, f_1, bc_mask, missing = st.prepare_fields()
     for i in range(steps):

@@ -282,6 +282,30 @@ def test_bulk_variant_many_steps_and_slab_ranges():
     assert torch.equal(f_1, g_1)
 
 
+def test_bulk_variant_concurrent_launches_on_two_streams():
+    """The persistent bulk kernel hands its tiles out through a pair of scheduler words in the library's static scratch; every
+    launch gets its own pair (round robin), so launches that overlap on the GPU -- two streams here, the edge / interior
+    branches of the multi-GPU schedule in general -- do not disturb each other, and the words are back at zero afterwards."""
+    case = cases.cavity3d(0, shape=(64, 48, 256), omega=1.6)
+    a, _ = build_product(case, backend_config={"kernel_variant": _lib.VARIANT_BULK})
+    f_0, f_1, bc_mask, missing = a.prepare_fields()
+    f_0.copy_(to_dev(cases.random_state(case, seed=21)))
+    ref, _ = build_product(case, backend_config={"kernel_variant": _lib.VARIANT_VECTOR})
+    r_1 = torch.zeros_like(f_1)
+    ref(f_0, r_1, bc_mask, missing, case["omega"], 0)
+    outs = [torch.zeros_like(f_1) for _ in range(4)]
+    streams = [torch.cuda.Stream() for _ in range(2)]
+    torch.cuda.synchronize()
+    for rep in range(3):
+        for k, out in enumerate(outs):
+            with torch.cuda.stream(streams[k % 2]):
+                a(f_0, out, bc_mask, missing, case["omega"], 0)
+        torch.cuda.synchronize()
+        for out in outs:
+            assert torch.equal(out, r_1)
+            out.zero_()
+
+
 # ----------------------------------------------------------------------------- BC cell list (XlbCollisionParams.bc_cells)
 LIST_CASES = [
     cases.sphere3d((48, 24, 24)),

@@ -54,7 +54,7 @@ class XlbStepRange(Structure):
 
 
 class XlbHaloPush(Structure):
-    _fields_ = [("peer_f1", c_void_p * 2), ("src", c_int32 * 2), ("dst", c_int32 * 2)]
+    _fields_ = [("peer_f1", c_void_p * 2), ("src", c_int32 * 2), ("dst", c_int32 * 2), ("peer_q_stride", c_int64 * 2)]
 
 
 class XlbBcEntry(Structure):

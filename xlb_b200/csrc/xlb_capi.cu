@@ -73,6 +73,42 @@ static unsigned blocks_for(long long n, int b) { return (unsigned)((n + b - 1) /
 
 using namespace xlb;
 
+// Tile-scheduler words of the persistent bulk kernel (xlb_step_bulk.cuh): XLB_SCHED_SLOTS pairs of zero-initialised counters;
+// every launch gets the next slot (round robin) and its last block puts the pair back to zero, so launches that overlap on
+// the GPU never share a pair unless more than XLB_SCHED_SLOTS launches are in flight at once.  (A launch captured in a CUDA
+// graph keeps its slot on every replay.)  The device address is resolved once per device with cudaGetSymbolAddress.
+#define XLB_SCHED_SLOTS 1024
+static __device__ __align__(256) unsigned g_step_sched[2 * XLB_SCHED_SLOTS];
+static std::atomic<unsigned> g_sched_next{0};
+
+static int step_sched_slot(unsigned** out) {
+    constexpr int MAX_DEV = 64;
+    static std::mutex mu;
+    static unsigned* cached[MAX_DEV] = {nullptr};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return count_launch(e);
+    if (dev < 0 || dev >= MAX_DEV) {  // beyond the cache: static stride
+        *out = nullptr;
+        return 0;
+    }
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (cached[dev] == nullptr) {
+            void* ptr = nullptr;
+            e = cudaGetSymbolAddress(&ptr, g_step_sched);
+            if (e != cudaSuccess || ptr == nullptr) {
+                std::snprintf(g_err, sizeof(g_err), "xlb_step: cudaGetSymbolAddress(g_step_sched) failed: %s", cudaGetErrorString(e));
+                cudaGetLastError();
+                return e != cudaSuccess ? (int)e : XLB_EINVAL;
+            }
+            cached[dev] = static_cast<unsigned*>(ptr);
+        }
+        *out = cached[dev] + 2 * (g_sched_next.fetch_add(1, std::memory_order_relaxed) % XLB_SCHED_SLOTS);
+    }
+    return 0;
+}
+
 extern "C" {
 
 const char* xlb_last_error(void) { return g_err; }
@@ -159,6 +195,8 @@ int xlb_step_range(const XlbDomain* dom, int collision, const XlbCollisionParams
             p.peer[k] = halo->peer_f1[k];
             p.peer_src[k] = halo->src[k];
             p.peer_off[k] = (long long)halo->dst[k] * unit;
+            p.peer_qs[k] = halo->peer_q_stride[k] ? halo->peer_q_stride[k] : p.qs;
+            if (p.peer_qs[k] < (long long)(halo->dst[k] + 1) * unit) return set_error(XLB_EINVAL, "xlb_step: XlbHaloPush.peer_q_stride is smaller than the ghost plane's offset");
         }
         if (p.peer[0] && p.peer[1] && p.peer_src[0] == p.peer_src[1])
             return set_error(XLB_EINVAL, "xlb_step: the slab must own at least two planes (first and last owned plane coincide)");
@@ -179,6 +217,7 @@ int xlb_step_range(const XlbDomain* dom, int collision, const XlbCollisionParams
         if (dom->d == 2) p.force3[0] = 0.0;
         collision |= XLB_COLL_FORCED;
     }
+    if (int rc = step_sched_slot(&p.sched)) return rc;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int key = dom->q * 100 + dom->compute_dtype * 10 + dom->store_dtype;
     switch (key) {

@@ -189,7 +189,11 @@ struct StepParams {
     // same q stride) at element offset peer_off[k] + (offset of the cell inside its plane / row)
     void* peer[2];
     long long peer_off[2];
+    long long peer_qs[2];  // population stride of that neighbour's buffer (its slab may be thicker or thinner than mine)
     int peer_src[2];
+    // tile scheduler of the persistent bulk kernel: two zero-initialised words in the library's static scratch
+    // ([0] next dynamic tile, [1] blocks finished), private to this launch; nullptr = static stride
+    unsigned* sched;
 };
 
 // slab axis of the multi-GPU decomposition in kernel axes: x for the 3-D lattices, y (= user x) for D2Q9, whose fields
@@ -200,20 +204,23 @@ XLB_HD constexpr int slab_axis() { return Q == 9 ? 1 : 0; }
 // where a thread's outgoing populations go on the neighbour (nullptr / c = 0: nowhere)
 template <typename S>
 struct PeerDst {
-    S* base;  // neighbour's population 0 at this thread's cell(s); population l is at base + l * qs
-    int c;    // lattice component along the slab axis that crosses this side: -1 or +1
+    S* base;       // neighbour's population 0 at this thread's cell(s); population l is at base + l * qs
+    long long qs;  // the NEIGHBOUR's population stride
+    int c;         // lattice component along the slab axis that crosses this side: -1 or +1
 };
 template <typename S, int Q>
 XLB_D PeerDst<S> peer_dst(const StepParams& p, int x, int y, long long offset_in_plane) {
-    PeerDst<S> d{nullptr, 0};
+    PeerDst<S> d{nullptr, 0, 0};
     if (p.peer[0] == nullptr && p.peer[1] == nullptr) return d;
     const int coord = slab_axis<Q>() == 0 ? x : y;
     const long long inner = slab_axis<Q>() == 0 ? offset_in_plane : offset_in_plane - (long long)y * p.nz;
     if (coord == p.peer_src[0] && p.peer[0] != nullptr) {
         d.base = static_cast<S*>(p.peer[0]) + (p.peer_off[0] + inner);
+        d.qs = p.peer_qs[0];
         d.c = -1;
     } else if (coord == p.peer_src[1] && p.peer[1] != nullptr) {
         d.base = static_cast<S*>(p.peer[1]) + (p.peer_off[1] + inner);
+        d.qs = p.peer_qs[1];
         d.c = 1;
     }
     return d;

@@ -125,7 +125,7 @@ XLB_D void cell_update_generic_impl(const StepParams& p, int x, int y, int z) {
         const S v = to_store<S, T>(f[l][0]);
         f1[l * p.qs + cell] = v;
         constexpr int ca = slab_c<Q>(Dir<Q, l>::cx, Dir<Q, l>::cy);
-        if (ca != 0 && pd.c == ca) pd.base[l * p.qs] = v;  // halo push: this population crosses into the neighbour's slab
+        if (ca != 0 && pd.c == ca) pd.base[l * pd.qs] = v;  // halo push: this population crosses into the neighbour's slab
     });
 }
 
@@ -343,7 +343,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_c
     }
     // ---- one aligned vector store per population (+ the halo push of the populations that leave the slab here)
     S* ql = f1 + cell;
-    PeerDst<S> pd{nullptr, 0};
+    PeerDst<S> pd{nullptr, 0, 0};
     if constexpr (PUSH) pd = peer_dst<S, Q>(p, x, y, (long long)y * p.nz + z0);
     S* qp = pd.base;
     static_for<Q>([&](auto lc) {
@@ -356,7 +356,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_c
         if constexpr (PUSH) {
             constexpr int ca = slab_c<Q>(Dir<Q, l>::cx, Dir<Q, l>::cy);
             if (ca != 0 && pd.c == ca) st_vec<S, V>(qp, o);
-            qp += p.qs;
+            qp += pd.qs;
         }
     });
 }

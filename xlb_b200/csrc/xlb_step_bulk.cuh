@@ -17,6 +17,14 @@
 #include "xlb_step.cuh"
 #include "xlb_step_h2.cuh"
 
+// 1: tiles are handed out dynamically (one atomicAdd on a global counter per tile) instead of by a static stride.  A tile
+// that holds cells of the per-cell engine (Zou-He / extrapolation planes) costs ~10 plain tiles; with a static stride the
+// launch ends when the unluckiest block does (BASELINE configs[2], 384x128x128: 256 of 888 blocks carry one such tile on top
+// of 55 plain ones -> +16 % on the kernel), with the counter the other blocks take over the rest of its share.
+#ifndef XLB_TUNE_DYN
+#define XLB_TUNE_DYN 1
+#endif
+
 namespace xlb {
 
 XLB_D uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
@@ -27,6 +35,9 @@ XLB_D void mbar_init(uint64_t* bar, uint32_t count) {
 XLB_D void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 XLB_D void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+XLB_D void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 // arrival counter of a stage: returns the previous value; acq_rel at CTA scope orders this warp's shared-memory reads of
 // the stage before the refill that the last-arriving warp issues
@@ -80,6 +91,10 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
     extern __shared__ __align__(128) unsigned char smem_raw[];
     uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + (size_t)STAGES * L::STAGE_BYTES);
     unsigned* arrived = reinterpret_cast<unsigned*>(full + STAGES);  // per stage: warps that have consumed it (monotonic)
+    int* tile_of = reinterpret_cast<int*>(arrived + STAGES);         // per stage: the tile staged there (-1: no more tiles)
+    int* tile_next = tile_of + STAGES;                                // per stage: the tile claimed for its NEXT refill (-1: none)
+    unsigned* exited = reinterpret_cast<unsigned*>(tile_next + STAGES);  // warps that have left the tile loop
+    const bool dyn = XLB_TUNE_DYN && p.sched != nullptr;
     constexpr unsigned NW = NT / 32;
     const S* __restrict__ f0 = static_cast<const S*>(p.f0);
     S* __restrict__ f1 = static_cast<S*>(p.f1);
@@ -110,12 +125,21 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
         x = p.x_begin + xr * p.x_stride;
     };
     // one warp (all 32 lanes): fetch tile t into stage s
+    // Halo of the z shift.  The packed-half2 consumer (H2) keeps the original scheme: one 16-byte chunk per shifted population
+    // next to the segment.  Otherwise the chunk is MERGED into the population's main copy (one copy of TZ + HE elements that
+    // starts HE elements early, or ends HE elements late) -- except at the two ends of a row, where the periodic neighbour is at
+    // the other end: a separate 16-byte copy there, or, when the row is one single tile (nseg == 1, e.g. the 128-wide
+    // BASELINE configs[2]), no halo copy at all: the neighbour is inside the staged row and the consumer wraps its index.
+    // Per tile this is Q + 1 bulk copies instead of Q + n_shifted + 1 (28 instead of 46 for D3Q27).
+    constexpr bool MERGE = !H2;
+    const bool one_seg = MERGE && nseg == 1;
+    const uint32_t tx_bytes = one_seg ? (uint32_t)(Q * TZ * sizeof(S) + L::MASK_BYTES) : L::TX_BYTES;
     auto issue = [&](int t, int s) {
         if (t >= total) return;
         int x, y, z0;
         tile_coords(t, x, y, z0);
         unsigned char* stage = smem_raw + (size_t)s * L::STAGE_BYTES;
-        if (lane == 0) mbar_arrive_expect_tx(&full[s], L::TX_BYTES);
+        if (lane == 0) mbar_arrive_expect_tx(&full[s], tx_bytes);
         __syncwarp();
         if (lane < Q) {
             int xs = x - lcx;
@@ -123,13 +147,23 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
             const int ys = wrap1(y - lcy, p.ny);
             const S* row = f0 + lane * p.qs + (xs * plane + (long long)ys * p.nz);
             S* dst = reinterpret_cast<S*>(stage) + lane * L::ROW;
-            bulk_g2s(dst + HE, row + z0, TZ * sizeof(S), &full[s]);
-            if (lcz == 1) {  // pull from z-1: the chunk left of the segment (periodic)
-                const int zs = (z0 == 0) ? p.nz - HE : z0 - HE;
-                bulk_g2s(dst, row + zs, 16, &full[s]);
-            } else if (lcz == -1) {  // pull from z+1: the chunk right of the segment (periodic)
-                const int zs = (z0 + TZ == p.nz) ? 0 : z0 + TZ;
-                bulk_g2s(dst + HE + TZ, row + zs, 16, &full[s]);
+            const bool first = z0 == 0, last = z0 + TZ == p.nz;
+            if (lcz == 0 || one_seg) {
+                bulk_g2s(dst + HE, row + z0, TZ * sizeof(S), &full[s]);
+            } else if (lcz == 1) {  // pull from z-1: HE elements left of the segment (periodic)
+                if (MERGE && !first) {
+                    bulk_g2s(dst, row + z0 - HE, (TZ + HE) * sizeof(S), &full[s]);
+                } else {
+                    bulk_g2s(dst + HE, row + z0, TZ * sizeof(S), &full[s]);
+                    bulk_g2s(dst, row + (first ? p.nz - HE : z0 - HE), 16, &full[s]);
+                }
+            } else {  // pull from z+1: HE elements right of the segment (periodic)
+                if (MERGE && !last) {
+                    bulk_g2s(dst + HE, row + z0, (TZ + HE) * sizeof(S), &full[s]);
+                } else {
+                    bulk_g2s(dst + HE, row + z0, TZ * sizeof(S), &full[s]);
+                    bulk_g2s(dst + HE + TZ, row + (last ? 0 : z0 + TZ), 16, &full[s]);
+                }
             }
         } else if (HAS_BC && lane == Q) {
             bulk_g2s(stage + L::POP_BYTES, p.bc_mask + (x * plane + (long long)y * p.nz + z0), TZ, &full[s]);
@@ -141,27 +175,76 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(&full[s], 1);
             arrived[s] = 0;
+            const long long t0 = (long long)blockIdx.x + (long long)s * gridDim.x;  // the first STAGES rounds are static
+            tile_of[s] = t0 < total ? (int)t0 : -1;
+            tile_next[s] = -1;
+            if (dyn && t0 < total) {  // the tile this stage gets at its first refill
+                const long long nt = (long long)STAGES * gridDim.x + atomicAdd(p.sched, 1u);
+                tile_next[s] = nt < total ? (int)nt : -1;
+            }
         }
+        *exited = 0;
         mbar_fence_init();
     }
     __syncthreads();
     if (tid < 32) {
 #pragma unroll
         for (int s = 0; s < STAGES; ++s) {
-            if ((long long)blockIdx.x + (long long)s * gridDim.x < total) issue((int)(blockIdx.x + s * gridDim.x), s);
+            if (tile_of[s] >= 0) issue(tile_of[s], s);
+            else if (dyn && lane == 0) mbar_arrive(&full[s]);  // nothing to stage: complete the phase so that nobody waits on it
         }
     }
+    // refill of stage s by the warp that consumed it last.  Static: the tile STAGES rounds ahead in the block's stride.  Dynamic:
+    // the tile in tile_next[s], which was claimed from the global counter at the previous refill of this stage; the claim for
+    // the refill after this one is issued right here (lane 0) but its result is only stored at the end of the iteration
+    // (flush_claim), so the atomic's round trip to L2 overlaps the collision instead of delaying the copies.  tile_of[s] /
+    // tile_next[s] are written before an arrive on the stage (release) and read after the wait / last arrival (acquire).
+    unsigned claim_val = 0;
+    int claim_stage = -1;
+    auto refill = [&](int t_done, int s) {
+        if (!dyn) {
+            if ((long long)t_done + (long long)STAGES * gridDim.x < total) issue(t_done + STAGES * (int)gridDim.x, s);
+            return;
+        }
+        const int nt = tile_next[s];
+        if (nt >= 0) {
+            if (lane == 0) tile_of[s] = nt;
+            issue(nt, s);
+            if (lane == 0) {
+                claim_val = atomicAdd(p.sched, 1u);
+                claim_stage = s;
+            }
+        } else if (lane == 0) {
+            tile_of[s] = -1;
+            mbar_arrive(&full[s]);
+        }
+    };
+    auto flush_claim = [&]() {
+        if (claim_stage >= 0) {
+            const long long nt = (long long)STAGES * gridDim.x + claim_val;
+            tile_next[claim_stage] = nt < total ? (int)nt : -1;
+            claim_stage = -1;
+        }
+    };
 
     const CollArgs<T> ca = coll_args<T>(p);
     int it = 0;
-    for (int t = blockIdx.x; t < total; t += gridDim.x, ++it) {
+    for (int t = blockIdx.x;; ++it) {
         const int s = it % STAGES;
         const uint32_t parity = (uint32_t)(it / STAGES) & 1u;
+        if (dyn) {
+            mbar_wait(&full[s], parity);
+            t = tile_of[s];
+            if (t < 0) break;
+        } else {
+            if (it > 0) t += gridDim.x;
+            if (t >= total) break;
+        }
         int x, y, z0;
         tile_coords(t, x, y, z0);
         const unsigned char* stage = smem_raw + (size_t)s * L::STAGE_BYTES;
         const S* pops = reinterpret_cast<const S*>(stage);
-        mbar_wait(&full[s], parity);
+        if (!dyn) mbar_wait(&full[s], parity);
         if constexpr (H2) {
             // ---- staged rows -> packed registers.  Pair k of thread t = cells z0 + 2t + k*2NT (+1); a pull shift of +-1
             // straddles two 32-bit words of the staged row: two conflict-free LDS.32 and one byte permute.
@@ -191,7 +274,7 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
             unsigned prev = 0;
             if (lane == 0) prev = stage_arrive(&arrived[s]);
             prev = __shfl_sync(0xffffffffu, prev, 0);
-            if ((prev + 1) % NW == 0 && (long long)t + (long long)STAGES * gridDim.x < total) issue(t + STAGES * (int)gridDim.x, s);
+            if ((prev + 1) % NW == 0) refill(t, s);
 
             static_for<W>([&](auto kc) {
                 XLB_IDX(k, kc);
@@ -279,6 +362,7 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
                     }
                 }
             });
+            flush_claim();
             continue;
         }
         // ---- staged rows -> registers (pull shift = index offset)
@@ -287,7 +371,12 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
             XLB_IDX(l, lc);
             constexpr int cz = Dir<Q, l>::cz;
 #pragma unroll
-            for (int j = 0; j < C; ++j) f[l][j] = to_compute<T, S>(pops[l * L::ROW + HE + tid + j * NT - cz]);
+            for (int j = 0; j < C; ++j) {
+                int idx = tid + j * NT - cz;
+                if (cz == 1 && j == 0) idx = (one_seg && idx < 0) ? TZ - 1 : idx;           // z = 0 pulls from z = nz - 1
+                if (cz == -1 && j == C - 1) idx = (one_seg && idx == TZ) ? 0 : idx;         // z = nz - 1 pulls from z = 0
+                f[l][j] = to_compute<T, S>(pops[l * L::ROW + HE + idx]);
+            }
         });
         uint8_t ids[C];
         bool any_bc = false;
@@ -304,7 +393,7 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
         unsigned prev = 0;
         if (lane == 0) prev = stage_arrive(&arrived[s]);
         prev = __shfl_sync(0xffffffffu, prev, 0);
-        if ((prev + 1) % NW == 0 && (long long)t + (long long)STAGES * gridDim.x < total) issue(t + STAGES * (int)gridDim.x, s);
+        if ((prev + 1) % NW == 0) refill(t, s);
 
         bool slow = false, any_half = false;
         bool k_full[C], k_eq[C], k_half[C];
@@ -331,6 +420,7 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
         const int zc = z0 + tid;
         if (HAS_BC && slow) {
             for (int j = 0; j < C; ++j) cell_update_generic<T, S, Q, COLL>(p, x, y, zc + j * NT);
+            flush_claim();
             continue;
         }
         if constexpr (HAS_BC && HALF) {
@@ -386,6 +476,24 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
 #pragma unroll
             for (int j = 0; j < C; ++j) ql[j * NT] = to_store<S, T>(f[l][j]);
             ql += p.qs;
+        }
+        flush_claim();
+    }
+    if (dyn) {
+        // the launch's last warp to leave puts the scheduler words back to zero for the next launch that gets this slot: every
+        // counter increment of a block precedes the exit of its last warp, every block's exit precedes the reset
+        __syncwarp();
+        if (lane == 0) {
+            unsigned left;
+            asm volatile("atom.acq_rel.cta.shared::cta.add.u32 %0, [%1], 1;" : "=r"(left) : "r"(smem_u32(exited)) : "memory");
+            if (left == NW - 1) {
+                __threadfence();
+                if (atomicAdd(p.sched + 1, 1u) == gridDim.x - 1) {
+                    __threadfence();
+                    p.sched[0] = 0u;
+                    p.sched[1] = 0u;
+                }
+            }
         }
     }
 }

@@ -26,6 +26,12 @@
 #define XLB_TUNE_STREAM_ONLY 0
 #endif
 
+// 1: the nine source-row addresses (c_x, c_y) of the pull are formed once per thread as byte pointers and every population's
+// load adds only the warp-uniform l * q_stride to one of them (2 integer instructions per load instead of ~6)
+#ifndef XLB_TUNE_H2_ROWPTR
+#define XLB_TUNE_H2_ROWPTR 0
+#endif
+
 namespace xlb {
 
 XLB_D uint32_t ld_if_u16(const void* ptr, bool pred, uint32_t keep) {
@@ -116,20 +122,26 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_h2_kernel(const __gri
 #pragma unroll
         for (int k = 0; k < (V + 3) / 4; ++k) any_bc |= idw[k] != 0;
         if (any_bc) {
+            // Only the tagged cells are decoded, one per trip of a rolled loop: in a cavity two warps of every row touch a wall
+            // cell at a z end, i.e. most warps come through here with ONE tagged cell in one or two lanes; decoding all V cells
+            // under predicates cost those warps ~150 instructions (ncu, profiles/r2b_ncu_details_f16.txt), this costs ~25.
+            uint32_t todo = 0;  // bit j: cell j is tagged
 #pragma unroll
-            for (int j = 0; j < V; ++j) {
-                const int id = id_of(j);
-                if (id) {
-                    const int k = p.bct[id].kind;
-                    m_full |= (k == XLB_BC_FULLWAY ? 1u : 0u) << j;
-                    m_eq |= (k == XLB_BC_EQUILIBRIUM ? 1u : 0u) << j;
-                    const bool here = p.cells == nullptr || !bc_is_listed(k);  // see step_vector_kernel
-                    if constexpr (HALF) {
-                        m_half |= (k == XLB_BC_HALFWAY ? 1u : 0u) << j;
-                        slow |= bc_is_complex(k) && k != XLB_BC_HALFWAY && here;
-                    } else {
-                        slow |= bc_is_complex(k) && here;
-                    }
+            for (int j = 0; j < V; ++j) todo |= (id_of(j) != 0 ? 1u : 0u) << j;
+#pragma unroll 1
+            while (todo) {
+                const int j = __ffs(todo) - 1;
+                todo &= todo - 1;
+                const uint32_t word = (V > 4 && j >= 4) ? idw[(V + 3) / 4 - 1] : idw[0];  // a select, not an indexed (local-memory) access
+                const int k = p.bct[(word >> (8 * (j & 3))) & 0xff].kind;
+                m_full |= (k == XLB_BC_FULLWAY ? 1u : 0u) << j;
+                m_eq |= (k == XLB_BC_EQUILIBRIUM ? 1u : 0u) << j;
+                const bool here = p.cells == nullptr || !bc_is_listed(k);  // see step_vector_kernel
+                if constexpr (HALF) {
+                    m_half |= (k == XLB_BC_HALFWAY ? 1u : 0u) << j;
+                    slow |= bc_is_complex(k) && k != XLB_BC_HALFWAY && here;
+                } else {
+                    slow |= bc_is_complex(k) && here;
                 }
             }
         }
@@ -148,12 +160,29 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_h2_kernel(const __gri
     PackedH2<Q, W> pk;
     uint32_t (&raw)[Q][W] = pk.w;
     const S* pl = f0;
+#if XLB_TUNE_H2_ROWPTR
+    const S* rowp[3][3];  // [c_x: 0, +1, -1][c_y: 0, +1, -1] -> population 0's source row
+    {
+        const long long oxs[3] = {ox0, oxm, oxp};
+        const int oys[3] = {oy0, oym, oyp};
+#pragma unroll
+        for (int a = 0; a < 3; ++a)
+#pragma unroll
+            for (int b = 0; b < 3; ++b) rowp[a][b] = f0 + (oxs[a] + oys[b]);
+    }
+    long long poff = 0;  // l * q_stride: the same for every thread of the grid (uniform datapath)
+#endif
     static_for<Q>([&](auto lc) {
         XLB_IDX(l, lc);
         using D = Dir<Q, l>;
+#if XLB_TUNE_H2_ROWPTR
+        const S* row = rowp[D::cx == 0 ? 0 : (D::cx == 1 ? 1 : 2)][D::cy == 0 ? 0 : (D::cy == 1 ? 1 : 2)] + poff;
+        poff += p.qs;
+#else
         const long long ox = D::cx == 0 ? ox0 : (D::cx == 1 ? oxm : oxp);
         const int oy = D::cy == 0 ? oy0 : (D::cy == 1 ? oym : oyp);
         const S* row = pl + (ox + oy);
+#endif
         const Words<W> v = ld_words<W>(row + z0);
         if (D::cz == 0) {
 #pragma unroll
@@ -250,7 +279,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_h2_kernel(const __gri
     if constexpr (!XLB_TUNE_STREAM_ONLY) static_for<W>([&](auto jc) { do_pair(jc, false); });
     // ---- one aligned vector store per population (+ the halo push of the populations that leave the slab here)
     S* ql = f1 + cell;
-    PeerDst<S> pd{nullptr, 0};
+    PeerDst<S> pd{nullptr, 0, 0};
     if constexpr (PUSH) pd = peer_dst<S, Q>(p, x, y, (long long)y * p.nz + z0);  // see step_vector_kernel
     S* qp = pd.base;
     static_for<Q>([&](auto lc) {
@@ -260,7 +289,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_h2_kernel(const __gri
         if constexpr (PUSH) {
             constexpr int ca = slab_c<Q>(Dir<Q, l>::cx, Dir<Q, l>::cy);
             if (ca != 0 && pd.c == ca) st_words<W>(qp, raw[l]);
-            qp += p.qs;
+            qp += pd.qs;
         }
     });
 }

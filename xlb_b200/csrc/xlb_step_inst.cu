@@ -195,7 +195,7 @@ static int step_main(const StepParams& p, int variant, cudaStream_t st) {
         bool ok = (p.nz % VMAX == 0) && (p.qs % VMAX == 0) && (b0 % (VMAX * sizeof(S)) == 0) && (b1 % (VMAX * sizeof(S)) == 0);
         if (has_bc) ok = ok && reinterpret_cast<uintptr_t>(p.bc_mask) % VMAX == 0 && reinterpret_cast<uintptr_t>(p.missing) % VMAX == 0 && p.mqs % VMAX == 0;
         for (int k = 0; k < 2; ++k)
-            if (p.peer[k]) ok = ok && reinterpret_cast<uintptr_t>(p.peer[k]) % (VMAX * sizeof(S)) == 0 && p.peer_off[k] % VMAX == 0;
+            if (p.peer[k]) ok = ok && reinterpret_cast<uintptr_t>(p.peer[k]) % (VMAX * sizeof(S)) == 0 && p.peer_off[k] % VMAX == 0 && p.peer_qs[k] % VMAX == 0;
         if (!ok || variant == XLB_VARIANT_SCALAR) return launch_generic<T, S, Q, COLL>(p, st);
         if (!has_bc) return launch_vector<T, S, Q, COLL, VMAX, false, false, true>(p, st);
         return half ? launch_vector<T, S, Q, COLL, VMAX, true, true, true>(p, st) : launch_vector<T, S, Q, COLL, VMAX, true, false, true>(p, st);

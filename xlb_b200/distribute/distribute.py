@@ -150,34 +150,37 @@ class PeerHalo:
         dev = buffers[0].device
         self.sync = torch.zeros(self.N_WORDS, dtype=torch.int64, device=dev)
         mine = [self.sync] + self.buffers
-        blob = torch.zeros((len(mine), 72), dtype=torch.uint8)
+        # per tensor: 64-byte IPC handle, byte offset inside its allocation, population stride (elements; ranks whose slabs
+        # differ in thickness have different strides, and the pushing kernel needs the RECEIVER's)
+        blob = torch.zeros((len(mine), 80), dtype=torch.uint8)
         for i, t in enumerate(mine):
             handle = (ctypes.c_ubyte * 64)()
             offset = ctypes.c_int64(0)
             _lib.check(lib.xlb_ipc_export(t.data_ptr(), handle, ctypes.byref(offset)), "xlb_ipc_export")
             blob[i, :64] = torch.frombuffer(bytearray(handle), dtype=torch.uint8)
-            blob[i, 64:] = torch.tensor([offset.value], dtype=torch.int64).view(torch.uint8)
+            blob[i, 64:] = torch.tensor([offset.value, t.stride(0) if t.dim() > 1 else 0], dtype=torch.int64).view(torch.uint8)
         blob = blob.to(dev)
         everyone = [torch.empty_like(blob) for _ in range(dec.world)]
         dist.all_gather(everyone, blob, group=dec.group)
         self._bases = {}  # handle bytes -> mapped base address (one cudaIpcOpenMemHandle per distinct allocation)
-        self.left = self._map(everyone[dec.left].cpu())
-        self.right = self._map(everyone[dec.right].cpu())
+        self.left, self.left_qs = self._map(everyone[dec.left].cpu())
+        self.right, self.right_qs = self._map(everyone[dec.right].cpu())
         dist.barrier(group=dec.group)  # nobody starts pushing before every mapping exists
 
     def _map(self, blob):
         lib = _lib.lib()
-        ptrs = []
+        ptrs, strides = [], []
         for row in blob:
             handle = bytes(row[:64].tolist())
-            offset = int(row[64:].view(torch.int64).item())
+            offset, stride = (int(v) for v in row[64:].view(torch.int64).tolist())
+            strides.append(stride)
             base = self._bases.get(handle)
             if base is None:
                 dptr, b = ctypes.c_void_p(), ctypes.c_void_p()
                 _lib.check(lib.xlb_ipc_import(handle, 0, ctypes.byref(dptr), ctypes.byref(b)), "xlb_ipc_import")
                 base = self._bases[handle] = b.value
             ptrs.append(base + offset)
-        return ptrs  # [sync, buffer 0, buffer 1, ...] of that neighbour
+        return ptrs, strides  # [sync, buffer 0, buffer 1, ...] of that neighbour
 
     def index_of(self, f):
         for i, b in enumerate(self.buffers):
@@ -192,6 +195,7 @@ class PeerHalo:
             return None
         h = _lib.XlbHaloPush()
         h.peer_f1[0], h.peer_f1[1] = self.left[1 + i], self.right[1 + i]
+        h.peer_q_stride[0], h.peer_q_stride[1] = self.left_qs[1 + i], self.right_qs[1 + i]
         h.src[0], h.src[1] = int(first_owned), int(last_owned)
         h.dst[0], h.dst[1] = self.ghost_dst
         return h
