@@ -745,8 +745,10 @@ def run_e2e(stepper, f_0, f_1, bc_mask, missing, omega, t, ncell, steps, chunk_p
 
     from xlb_b200.operator.stepper import HostStreamedStepper
 
-    h_in = torch.empty(f_0.shape, dtype=f_0.dtype, pin_memory=True)
-    h_out = torch.empty(f_1.shape, dtype=f_1.dtype, pin_memory=True)
+    from xlb_b200.helper.host_memory import pinned_empty
+
+    h_in, placement = pinned_empty(f_0.shape, f_0.dtype)
+    h_out, _ = pinned_empty(f_1.shape, f_1.dtype)
     h_in.copy_(f_0)
     torch.cuda.synchronize()
     hs = HostStreamedStepper(stepper, chunk_planes=chunk_planes)
@@ -774,6 +776,7 @@ def run_e2e(stepper, f_0, f_1, bc_mask, missing, omega, t, ncell, steps, chunk_p
         "d2h_bytes_per_step": int(nbytes),
         "steps": steps,
         "ms_per_step": ms / steps,
+        "host_memory": placement,
         "note": f"HostStreamedStepper: pinned-host populations, {len(hs._state['chunks'])} x-chunks of {hs._state['P']} planes pipelined over h2d / compute / d2h streams; finite={probe == probe}",
     }
 

@@ -88,6 +88,10 @@ typedef struct XlbCollisionParams {
                                 outflow).  When given, the fused kernel leaves those cells to a second, dense launch over the list
                                 instead of diverging into the per-cell engine; NULL = handle them inside the fused kernel */
     int64_t n_bc_cells;      /* entries of bc_cells */
+    const uint32_t* missing_bits; /* optional device array [nx*ny*nz] from xlb_pack_missing: bit l of word `cell` = missing_mask[l][cell].
+                                The boundary paths that need a cell's missing directions (half-way, Zou-He, regularized,
+                                extrapolation) then read ONE word per cell instead of q bytes from q planes; NULL = read the bytes.
+                                Must describe the same missing_mask that is passed to the call; 16-byte aligned */
 } XlbCollisionParams;
 
 /* Which planes (and, for the 2-D slab decomposition, which rows of each plane) one launch updates: planes
@@ -117,6 +121,7 @@ const char* xlb_last_error(void);
 int xlb_abi_version(void);
 int xlb_bc_entry_size(void);
 int xlb_domain_size(void);
+int xlb_collision_params_size(void);
 /* number of kernels this library has launched from the calling process (for bench gpu_launches) */
 long long xlb_launch_count(void);
 
@@ -211,6 +216,11 @@ int xlb_mask_tag(const XlbDomain* dom, const int32_t* indices, int64_t n, const 
                  int mark_solid, int pad, uint8_t* bc_mask, uint8_t* solid, void* stream);
 int xlb_mask_missing(const XlbDomain* dom, const uint8_t* solid, const int32_t origin[3], const int32_t global_shape[3],
                      uint8_t* missing_mask, void* stream);
+
+/* missing_mask [q][N] (bool / uint8 planes, indices_boundary_masker.py:134-143) -> one uint32 per cell, bit l = missing[l] (SURVEY
+ * 8(b) `xlb_pack_missing`; Appendix A: "a packed uint32 bitfield used by kernels").  Setup-time helper for
+ * XlbCollisionParams.missing_bits; rerun it whenever missing_mask changes. */
+int xlb_pack_missing(const XlbDomain* dom, const uint8_t* missing_mask, uint32_t* missing_bits, void* stream);
 
 /* Allocation-free variant of the indices masker (xlb_mask_tag + xlb_mask_missing above).  NO COUNTERPART IN THE REFERENCE: added
  * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving

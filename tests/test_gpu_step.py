@@ -401,6 +401,34 @@ def test_bc_cell_list_follows_mask_updates():
     assert torch.equal(f_1, g_1)
 
 
+@pytest.mark.parametrize("case", [cases.sphere3d((48, 24, 24)), cases.sphere3d((28, 16, 256)), cases.sphere3d((48, 24, 24), policy="FP32FP16"),
+                                  cases.sphere3d((40, 24, 20), lattice="D3Q19", collision="BGK", policy="FP64FP64", inlet="pressure", outlet="pressure"),
+                                  cases.cavity2d(24, collision="KBC")], ids=lambda c: c["name"])
+def test_packed_missing_bits_equal_byte_planes(case):
+    """xlb_pack_missing: bit l of word `cell` == missing_mask[l][cell]; and the step with XlbCollisionParams.missing_bits (the
+    default) == the step that reads the q byte planes, bitwise, for the fused kernels and the BC cell list kernel."""
+    a, _ = build_product(case, backend_config={"bc_cell_list": True})
+    f_0, f_1, bc_mask, missing = a.prepare_fields()
+    bits = a._mbits[1]
+    assert bits is not None and bits.dtype == torch.int32 and tuple(bits.shape) == tuple(missing.shape[1:])
+    mm = to_np(missing).astype(np.uint32)
+    want = np.zeros(mm.shape[1:], dtype=np.uint32)
+    for l in range(mm.shape[0]):
+        want |= mm[l] << np.uint32(l)
+    assert np.array_equal(to_np(bits).view(np.uint32), want)
+    f_0.copy_(to_dev(cases.random_state(case, seed=13)))
+    b, _ = build_product(case, backend_config={"bc_cell_list": True, "packed_missing": False})
+    g_0, g_1, bc_b, mm_b = b.prepare_fields()
+    assert b._mbits[1] is None
+    g_0.copy_(f_0)
+    for i in range(4):
+        f_0, f_1 = a(f_0, f_1, bc_mask, missing, case["omega"], i)
+        f_0, f_1 = f_1, f_0
+        g_0, g_1 = b(g_0, g_1, bc_b, mm_b, case["omega"], i)
+        g_0, g_1 = g_1, g_0
+    assert torch.equal(f_0, g_0)
+
+
 def test_bc_cell_list_follows_remasking_through_the_c_abi():
     """The maskers write bc_mask through raw pointers (invisible to torch's version counter): re-running a masker on the
     same tensor must still invalidate the cached list."""

@@ -46,6 +46,7 @@ class XlbCollisionParams(Structure):
         ("halfway_fraction", c_double),
         ("bc_cells", c_void_p),
         ("n_bc_cells", c_int64),
+        ("missing_bits", c_void_p),
     ]
 
 
@@ -89,6 +90,7 @@ EXPORTS = {
     "xlb_abi_version": (c_int, []),
     "xlb_bc_entry_size": (c_int, []),
     "xlb_domain_size": (c_int, []),
+    "xlb_collision_params_size": (c_int, []),
     "xlb_launch_count": (c_longlong, []),
     "xlb_step": (c_int, [POINTER(XlbDomain), c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_double, c_int, c_int, c_int, c_int, c_void_p]),
     "xlb_step_ex": (c_int, [POINTER(XlbDomain), c_int, POINTER(XlbCollisionParams), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_double, c_int, c_int, c_int, c_int, c_void_p]),
@@ -99,6 +101,7 @@ EXPORTS = {
     "xlb_ipc_import": (c_int, [c_void_p, c_int64, POINTER(c_void_p), POINTER(c_void_p)]),
     "xlb_ipc_close": (c_int, [c_void_p]),
     "xlb_copy_runs": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int, c_void_p]),
+    "xlb_pack_missing": (c_int, [POINTER(XlbDomain), c_void_p, c_void_p, c_void_p]),
     "xlb_list_bc_cells": (c_int, [POINTER(XlbDomain), c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p]),
     "xlb_stream": (c_int, [POINTER(XlbDomain), c_int, c_void_p, c_void_p, c_void_p]),
     "xlb_macroscopic": (c_int, [POINTER(XlbDomain), c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
@@ -139,6 +142,8 @@ def lib():
         raise RuntimeError(f"{LIB_PATH}: ABI version {handle.xlb_abi_version()} != expected {ABI_VERSION}; rebuild")
     if handle.xlb_bc_entry_size() != ctypes.sizeof(XlbBcEntry) or handle.xlb_bc_entry_size() != BC_ENTRY_DTYPE.itemsize:
         raise RuntimeError("XlbBcEntry layout mismatch between the library and the Python binding")
+    if not partial and handle.xlb_collision_params_size() != ctypes.sizeof(XlbCollisionParams):
+        raise RuntimeError("XlbCollisionParams layout mismatch between the library and the Python binding")
     if handle.xlb_domain_size() != ctypes.sizeof(XlbDomain):
         raise RuntimeError("XlbDomain layout mismatch between the library and the Python binding")
     _lib = handle

@@ -115,6 +115,7 @@ const char* xlb_last_error(void) { return g_err; }
 int xlb_abi_version(void) { return XLB_B200_ABI_VERSION; }
 int xlb_bc_entry_size(void) { return (int)sizeof(XlbBcEntry); }
 int xlb_domain_size(void) { return (int)sizeof(XlbDomain); }
+int xlb_collision_params_size(void) { return (int)sizeof(XlbCollisionParams); }
 long long xlb_launch_count(void) { return g_launches.load(); }
 
 int xlb_step(const XlbDomain* dom, int collision, const void* f0, void* f1, const uint8_t* bc_mask, const uint8_t* missing_mask,
@@ -200,6 +201,10 @@ int xlb_step_range(const XlbDomain* dom, int collision, const XlbCollisionParams
         }
         if (p.peer[0] && p.peer[1] && p.peer_src[0] == p.peer_src[1])
             return set_error(XLB_EINVAL, "xlb_step: the slab must own at least two planes (first and last owned plane coincide)");
+    }
+    if (cp && cp->missing_bits && has_bc) {
+        if (reinterpret_cast<uintptr_t>(cp->missing_bits) % 16 != 0) return set_error(XLB_EALIGN, "xlb_step: missing_bits must be 16-byte aligned");
+        p.mbits = cp->missing_bits;
     }
     if (cp && cp->bc_cells) {
         if (cp->n_bc_cells < 0 || cp->n_bc_cells >= (1ll << 37)) return set_error(XLB_EINVAL, "xlb_step: bad n_bc_cells");
@@ -541,6 +546,19 @@ int xlb_mask_missing(const XlbDomain* dom, const uint8_t* solid, const int32_t o
     if (dom->q == 9) mask_missing_kernel<9><<<nb, 256, 0, st>>>(p);
     else if (dom->q == 19) mask_missing_kernel<19><<<nb, 256, 0, st>>>(p);
     else mask_missing_kernel<27><<<nb, 256, 0, st>>>(p);
+    return count_launch(cudaGetLastError());
+}
+
+int xlb_pack_missing(const XlbDomain* dom, const uint8_t* missing_mask, uint32_t* missing_bits, void* stream) {
+    if (int rc = check_domain(dom, "xlb_pack_missing")) return rc;
+    if (!missing_mask || !missing_bits) return set_error(XLB_EINVAL, "xlb_pack_missing: null pointer");
+    const long long ncell = (long long)dom->nx * dom->ny * dom->nz;
+    const long long mqs = dom->mask_q_stride ? dom->mask_q_stride : ncell;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const unsigned nb = blocks_for(ncell, 256);
+    if (dom->q == 9) pack_missing_kernel<9><<<nb, 256, 0, st>>>(missing_mask, mqs, ncell, missing_bits);
+    else if (dom->q == 19) pack_missing_kernel<19><<<nb, 256, 0, st>>>(missing_mask, mqs, ncell, missing_bits);
+    else pack_missing_kernel<27><<<nb, 256, 0, st>>>(missing_mask, mqs, ncell, missing_bits);
     return count_launch(cudaGetLastError());
 }
 

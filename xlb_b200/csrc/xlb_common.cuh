@@ -194,6 +194,8 @@ struct StepParams {
     // tile scheduler of the persistent bulk kernel: two zero-initialised words in the library's static scratch
     // ([0] next dynamic tile, [1] blocks finished), private to this launch; nullptr = static stride
     unsigned* sched;
+    // XlbCollisionParams.missing_bits: missing_mask packed to one word per cell (bit l = missing[l]); nullptr = read the q bytes
+    const uint32_t* mbits;
 };
 
 // slab axis of the multi-GPU decomposition in kernel axes: x for the 3-D lattices, y (= user x) for D2Q9, whose fields

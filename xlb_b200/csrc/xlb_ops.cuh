@@ -302,6 +302,17 @@ struct MaskParams {
     long long mqs;
 };
 
+// missing_mask planes -> one word per cell (XlbCollisionParams.missing_bits)
+template <int Q>
+__global__ void __launch_bounds__(256) pack_missing_kernel(const uint8_t* __restrict__ missing, long long mqs, long long ncell, uint32_t* __restrict__ bits) {
+    const long long cell = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (cell >= ncell) return;
+    uint32_t m = 0;
+#pragma unroll
+    for (int l = 0; l < Q; ++l) m |= (missing[l * mqs + cell] ? 1u : 0u) << l;
+    bits[cell] = m;
+}
+
 // indices_boundary_masker.py:107-128: tag bc ids (optionally on the padded set index + c_l) and solid cells
 template <int Q>
 __global__ void __launch_bounds__(256) mask_tag_kernel(const __grid_constant__ MaskParams p) {

@@ -68,8 +68,12 @@ XLB_D void cell_update_generic_impl(const StepParams& p, int x, int y, int z) {
     });
     uint32_t miss = 0;
     if (kind >= XLB_BC_HALFWAY && kind != XLB_BC_DONOTHING) {
+        if (p.mbits) {
+            miss = p.mbits[cell];
+        } else {
 #pragma unroll
-        for (int l = 0; l < Q; ++l) miss |= (p.missing[l * p.mqs + cell] ? 1u : 0u) << l;
+            for (int l = 0; l < Q; ++l) miss |= (p.missing[l * p.mqs + cell] ? 1u : 0u) << l;
+        }
     }
     // ---- STREAMING-step boundary conditions (nse_stepper.py:250-257)
     if (kind == XLB_BC_EQUILIBRIUM) {
@@ -299,12 +303,18 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_c
             uint32_t mb[V];
 #pragma unroll
             for (int j = 0; j < V; ++j) mb[j] = 0;
-            static_for<Q>([&](auto lc) {
-                XLB_IDX(l, lc);
-                const Vec<uint8_t, V> m = ld_vec<uint8_t, V>(p.missing + l * p.mqs + cell);
+            if (p.mbits) {  // one vector load of the packed words instead of q byte-plane loads
+                const Vec<uint32_t, V> m = ld_vec<uint32_t, V>(p.mbits + cell);
 #pragma unroll
-                for (int j = 0; j < V; ++j) mb[j] |= (m.v[j] ? 1u : 0u) << l;
-            });
+                for (int j = 0; j < V; ++j) mb[j] = m.v[j];
+            } else {
+                static_for<Q>([&](auto lc) {
+                    XLB_IDX(l, lc);
+                    const Vec<uint8_t, V> m = ld_vec<uint8_t, V>(p.missing + l * p.mqs + cell);
+#pragma unroll
+                    for (int j = 0; j < V; ++j) mb[j] |= (m.v[j] ? 1u : 0u) << l;
+                });
+            }
 #pragma unroll
             for (int j = 0; j < V; ++j)
                 if (!k_half[j]) mb[j] = 0;

@@ -317,12 +317,18 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
                         if constexpr (HAS_BC && HALF) {
                             if (hf[0] || hf[1]) {  // HalfwayBounceBackBC, STREAMING step (bc_halfway_bounce_back.py:116-134)
                                 uint32_t mb[2] = {0, 0};
-                                static_for<Q>([&](auto lc) {
-                                    XLB_IDX(l, lc);
-                                    const Vec<uint8_t, 2> m = ld_vec<uint8_t, 2>(p.missing + l * p.mqs + cell0);
-                                    mb[0] |= (m.v[0] ? 1u : 0u) << l;
-                                    mb[1] |= (m.v[1] ? 1u : 0u) << l;
-                                });
+                                if (p.mbits) {
+                                    const Vec<uint32_t, 2> m = ld_vec<uint32_t, 2>(p.mbits + cell0);
+                                    mb[0] = m.v[0];
+                                    mb[1] = m.v[1];
+                                } else {
+                                    static_for<Q>([&](auto lc) {
+                                        XLB_IDX(l, lc);
+                                        const Vec<uint8_t, 2> m = ld_vec<uint8_t, 2>(p.missing + l * p.mqs + cell0);
+                                        mb[0] |= (m.v[0] ? 1u : 0u) << l;
+                                        mb[1] |= (m.v[1] ? 1u : 0u) << l;
+                                    });
+                                }
                                 if (!hf[0]) mb[0] = 0;
                                 if (!hf[1]) mb[1] = 0;
                                 const double* tab0 = p.bct[id2[0]].table;
@@ -431,11 +437,16 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
                 uint32_t mb[C];
 #pragma unroll
                 for (int j = 0; j < C; ++j) mb[j] = 0;
-                static_for<Q>([&](auto lc) {
-                    XLB_IDX(l, lc);
+                if (p.mbits) {
 #pragma unroll
-                    for (int j = 0; j < C; ++j) mb[j] |= (p.missing[l * p.mqs + cell0 + j * NT] ? 1u : 0u) << l;
-                });
+                    for (int j = 0; j < C; ++j) mb[j] = p.mbits[cell0 + j * NT];
+                } else {
+                    static_for<Q>([&](auto lc) {
+                        XLB_IDX(l, lc);
+#pragma unroll
+                        for (int j = 0; j < C; ++j) mb[j] |= (p.missing[l * p.mqs + cell0 + j * NT] ? 1u : 0u) << l;
+                    });
+                }
 #pragma unroll
                 for (int j = 0; j < C; ++j)
                     if (!k_half[j]) mb[j] = 0;

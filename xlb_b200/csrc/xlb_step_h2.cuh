@@ -236,12 +236,18 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_h2_kernel(const __gri
                 if (m_half & PAIR) {
                     // HalfwayBounceBackBC, STREAMING step (bc_halfway_bounce_back.py:116-134), see step_vector_kernel
                     uint32_t mb[2] = {0, 0};
-                    static_for<Q>([&](auto lc) {
-                        XLB_IDX(l, lc);
-                        const Vec<uint8_t, 2> m = ld_vec<uint8_t, 2>(p.missing + l * p.mqs + cell + 2 * jp);
-                        mb[0] |= (m.v[0] ? 1u : 0u) << l;
-                        mb[1] |= (m.v[1] ? 1u : 0u) << l;
-                    });
+                    if (p.mbits) {
+                        const Vec<uint32_t, 2> m = ld_vec<uint32_t, 2>(p.mbits + cell + 2 * jp);
+                        mb[0] = m.v[0];
+                        mb[1] = m.v[1];
+                    } else {
+                        static_for<Q>([&](auto lc) {
+                            XLB_IDX(l, lc);
+                            const Vec<uint8_t, 2> m = ld_vec<uint8_t, 2>(p.missing + l * p.mqs + cell + 2 * jp);
+                            mb[0] |= (m.v[0] ? 1u : 0u) << l;
+                            mb[1] |= (m.v[1] ? 1u : 0u) << l;
+                        });
+                    }
                     if (!((m_half >> (2 * jp)) & 1u)) mb[0] = 0;
                     if (!((m_half >> (2 * jp + 1)) & 1u)) mb[1] = 0;
                     const double* tab0 = p.bct[id_of(2 * jp)].table;

@@ -127,6 +127,7 @@ static int try_bulk(const StepParams& p, cudaStream_t st) {
     bool aligned = (a0 % 16 == 0) && ((p.qs * sizeof(S)) % 16 == 0) && ((p.nz * sizeof(S)) % 16 == 0) && (!HAS_BC || am % 16 == 0);
     // the half-way path of the packed-half2 consumer reads the missing bytes of a cell pair with one 16-bit load
     if (HAS_BC && sizeof(S) == 2) aligned = aligned && reinterpret_cast<uintptr_t>(p.missing) % 2 == 0 && p.mqs % 2 == 0;
+    if (HAS_BC) aligned = aligned && reinterpret_cast<uintptr_t>(p.mbits) % 8 == 0;
     if (p.peer[0] || p.peer[1]) return -1000;  // halo push: the vector kernel's PUSH instance
     if (!aligned) return -1000;
     if constexpr (XLB_TUNE_H2 && std::is_same<S, __half>::value && std::is_same<T, float>::value) {
@@ -193,7 +194,8 @@ static int step_main(const StepParams& p, int variant, cudaStream_t st) {
         // the full vector width, else the generic kernel (every variant performs the same arithmetic, bit for bit)
         const uintptr_t b0 = reinterpret_cast<uintptr_t>(p.f0), b1 = reinterpret_cast<uintptr_t>(p.f1);
         bool ok = (p.nz % VMAX == 0) && (p.qs % VMAX == 0) && (b0 % (VMAX * sizeof(S)) == 0) && (b1 % (VMAX * sizeof(S)) == 0);
-        if (has_bc) ok = ok && reinterpret_cast<uintptr_t>(p.bc_mask) % VMAX == 0 && reinterpret_cast<uintptr_t>(p.missing) % VMAX == 0 && p.mqs % VMAX == 0;
+        if (has_bc) ok = ok && reinterpret_cast<uintptr_t>(p.bc_mask) % VMAX == 0 && reinterpret_cast<uintptr_t>(p.missing) % VMAX == 0 && p.mqs % VMAX == 0 &&
+                         reinterpret_cast<uintptr_t>(p.mbits) % (4 * VMAX) == 0;
         for (int k = 0; k < 2; ++k)
             if (p.peer[k]) ok = ok && reinterpret_cast<uintptr_t>(p.peer[k]) % (VMAX * sizeof(S)) == 0 && p.peer_off[k] % VMAX == 0 && p.peer_qs[k] % VMAX == 0;
         if (!ok || variant == XLB_VARIANT_SCALAR) return launch_generic<T, S, Q, COLL>(p, st);
@@ -213,15 +215,19 @@ static int step_main(const StepParams& p, int variant, cudaStream_t st) {
     // the vectorised paths move V bc_mask / missing_mask bytes and V populations per access: every base pointer and stride
     // must be aligned to the vector
     const uintptr_t am = reinterpret_cast<uintptr_t>(p.missing);
-    auto masks_ok = [&](int v) { return !has_bc || (reinterpret_cast<uintptr_t>(p.bc_mask) % v == 0 && am % v == 0 && p.mqs % v == 0); };
+    auto masks_ok = [&](int v) {
+        return !has_bc || (reinterpret_cast<uintptr_t>(p.bc_mask) % v == 0 && am % v == 0 && p.mqs % v == 0 &&
+                           reinterpret_cast<uintptr_t>(p.mbits) % (4 * v) == 0);
+    };
     const bool vec_ok = (p.nz % VMAX == 0) && (p.qs % VMAX == 0) && (a0 % (VMAX * sizeof(S)) == 0) && (a1 % (VMAX * sizeof(S)) == 0) &&
                         masks_ok(VMAX);
     if (variant == XLB_VARIANT_VECTOR && !vec_ok && !(VMAX == 8 && p.nz % 4 == 0)) return set_error(XLB_EALIGN, "xlb_step: vector variant needs nz, q_stride and base pointers aligned to the vector width");
     // AUTO: the bulk-staged pipeline where the B200 sweeps show it ahead of the vector kernel (D3Q27 KBC, compute-heavy)
     if constexpr (Q == 27 && COLL == XLB_KBC && sizeof(S) == 4) {
-        // ... except on blocks where a large half-way obstacle covers more than ~1 % of the cells: the direct loads of its
-        // bounce-back path are latency-exposed at the pipeline's low occupancy, the vector kernel hides them better
-        if (variant == XLB_VARIANT_AUTO && !(half && p.halfway_fraction > 0.01f)) {
+        // (round 1 fell back to the vector kernel on blocks where a half-way obstacle covers more than ~1 % of the cells; with the
+        // dynamic tile scheduler and the packed missing bits the pipeline is ahead there too: 22.7k vs 21.1k MLUPS on a
+        // 192x1536x1536 block holding half of an r = 192 sphere)
+        if (variant == XLB_VARIANT_AUTO) {
             const int rc = bulk();
             if (rc != -1000) return rc;
         }

@@ -64,6 +64,7 @@ class HostStreamedStepper:
         cp = _lib.XlbCollisionParams()
         ctypes.memmove(ctypes.byref(cp), ctypes.byref(st._collision_params), ctypes.sizeof(cp))
         cp.bc_cells, cp.n_bc_cells = None, 0
+        cp.missing_bits = None  # the packed words are indexed by the resident block's cells as well
         cp.halfway_fraction = 0.0
         self._state = dict(shape=tuple(f_host.shape), P=P, cp=cp, bufs_in=bufs_in, bufs_out=bufs_out, streams=streams, table=table, n_bc=n_bc,
                            chunks=chunks,

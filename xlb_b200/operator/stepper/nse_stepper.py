@@ -65,6 +65,7 @@ class IncompressibleNavierStokesStepper(Stepper):
         self._plan = None  # (key, domain struct, bc table tensor, n_bc)
         # BC cell list (XlbCollisionParams.bc_cells): (key, sorted cell indices on the device, per-plane offsets on the host)
         self._cells = None
+        self._mbits = None  # (key, missing_mask packed to one uint32 per cell)
         # backend_config["bc_cell_list"]: True / False force it; "auto" (default) uses it when the block holds enough such
         # cells for the second launch to pay for itself (B200: ~1e5 cells; below that the in-kernel path is ahead,
         # profiles/r1q_*: 384x128x128 sphere 22.4k -> 21.6k MLUPS with the list, 192x1536x1536 wind tunnel 21.5k -> 23.9k)
@@ -94,6 +95,7 @@ class IncompressibleNavierStokesStepper(Stepper):
                 f_0 = initialize_eq(f_0, self.grid, self.velocity_set, self.precision_policy, self.compute_backend)
         if self.boundary_conditions:
             self._bc_cell_list(f_0, bc_mask)  # built here so that the step loop itself never synchronises
+            self._missing_bits(f_0, missing_mask)
         return f_0, f_1, bc_mask, missing_mask
 
     def _halfway_fraction(self, bc_mask):
@@ -213,10 +215,33 @@ class IncompressibleNavierStokesStepper(Stepper):
         self._cells = (key, cells, offsets)
         return self._cells
 
+    _NEEDS_MISSING = (_lib.BC_HALFWAY, _lib.BC_ZOUHE_VELOCITY, _lib.BC_ZOUHE_PRESSURE, _lib.BC_EXTRAPOLATION,
+                      _lib.BC_REGULARIZED_VELOCITY, _lib.BC_REGULARIZED_PRESSURE)
+
+    def _missing_bits(self, f_0, missing_mask):
+        """``missing_mask`` packed to one uint32 per cell (``XlbCollisionParams.missing_bits``, ``xlb_pack_missing``) for the
+        boundary paths that need a cell's missing directions: one load instead of q byte loads from q planes.  Built once per
+        mask content (same cache rule as the BC cell list); ``backend_config["packed_missing"] = False`` turns it off."""
+        key = (missing_mask.data_ptr(), missing_mask._version, getattr(missing_mask, "_xlb_generation", None), tuple(missing_mask.shape))
+        if self._mbits is not None and self._mbits[0] == key:
+            return self._mbits[1]
+        self._mbits = (key, None)
+        wanted = self.backend_config.get("packed_missing", True) if self.backend_config else True
+        if os.environ.get("XLB_B200_PACKED_MISSING") in ("0", "1") and not (self.backend_config and "packed_missing" in self.backend_config):
+            wanted = os.environ["XLB_B200_PACKED_MISSING"] == "1"  # experiments, like XLB_B200_BC_CELL_LIST
+        if not wanted or not any(int(bc.abi_kind) in self._NEEDS_MISSING for bc in self.boundary_conditions):
+            return None
+        _, dom, _, _, _, _ = self._get_plan(f_0)
+        bits = torch.empty(tuple(missing_mask.shape[1:]), dtype=torch.int32, device=missing_mask.device)
+        check(lib().xlb_pack_missing(byref(dom), missing_mask.data_ptr(), bits.data_ptr(), stream_ptr()), "IncompressibleNavierStokesStepper")
+        self._mbits = (key, bits)
+        return bits
+
     def invalidate_bc_cells(self):
-        """Forget the cached BC cell list.  Needed only after ``bc_mask`` was rewritten behind torch's back (a raw-pointer
+        """Forget the cached BC cell list and packed missing bits.  Needed only after ``bc_mask`` was rewritten behind torch's back (a raw-pointer
         write from foreign code); torch in-place ops and this package's maskers are noticed automatically."""
         self._cells = None
+        self._mbits = None
 
     # ------------------------------------------------------------------ the step
     def launch_range(self, f_0, f_1, bc_mask, missing_mask, omega, timestep, x_begin, x_end):
@@ -245,6 +270,11 @@ class IncompressibleNavierStokesStepper(Stepper):
             self._check_field(missing_mask, "missing_mask", q)
         cp = self._collision_params
         cp.bc_cells, cp.n_bc_cells = None, 0
+        cp.missing_bits = None
+        if n_bc:
+            bits = self._missing_bits(f_0, missing_mask)
+            if bits is not None:
+                cp.missing_bits = bits.data_ptr()
         if n_bc and rng.n_planes > 0:
             _, cells, offsets = self._bc_cell_list(f_0, bc_mask)
             if cells is not None:
