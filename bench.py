@@ -44,6 +44,8 @@ WORKLOADS = {
     "cavity768_d3q19_bgk_fp16": ("D3Q19", "BGK", "FP32FP16", (512, 768, 768), 1.0, "cavity"),
     "cavity512_d3q19_bgk_fp16": ("D3Q19", "BGK", "FP32FP16", (512, 512, 512), 1.0, "cavity"),
     "cavity1024_d3q19_bgk_fp16": ("D3Q19", "BGK", "FP32FP16", (1024, 1024, 1024), 1.0, "cavity"),
+    # 1024^3 in FP32: 81.6 GB per population buffer -- one B200 holds it only with --in-place (one buffer, the AA pattern)
+    "cavity1024_d3q19_bgk_fp32": ("D3Q19", "BGK", "FP32FP32", (1024, 1024, 1024), 1.0, "cavity"),
     "cavity640_d3q19_bgk_fp16": ("D3Q19", "BGK", "FP32FP16", (640, 640, 640), 1.0, "cavity"),
     # BASELINE configs[4] (windtunnel_3d.py with a sphere instead of the STL car): 1536 x 1536 cross-section,
     # 192 planes per GPU (weak scaling: 1536^3 on 8 GPUs); omega from Re = 50 000 like windtunnel_3d.py:42-45
@@ -522,7 +524,8 @@ def run_native(args):
         shape = tuple(shape) if shape else shape0
         if world > 1 and not strong:
             shape = (shape[0] * world,) + tuple(shape[1:])  # weak scaling: the N=1 block per GPU, stacked along x
-        stepper, vs, pol, shape, omega = build_case(workload, slab=slab, shape=shape, variant=args.variant, radius=args.radius)
+        stepper, vs, pol, shape, omega = build_case(workload, slab=slab, shape=shape, variant=args.variant, radius=args.radius,
+                                                    backend_config={"in_place": True} if args.in_place else None)
         if slab is not None:
             from xlb_b200.distribute import distribute
 
@@ -643,7 +646,7 @@ def run_native(args):
 
     # ---- e2e: HOST buffers in, HOST buffers out (pinned), copies inside the timed region
     e2e = e2e_resident = None
-    if world == 1 and not args.no_e2e:
+    if world == 1 and not args.no_e2e and not args.in_place:
         e2e = run_e2e(stepper, f_0, f_1, bc_mask, missing, omega, t, ncell, max(1, min(args.steps, args.e2e_steps)))
         e2e_resident = run_resident_api(stepper, f_0, f_1, bc_mask, missing, omega, t, ncell, min(args.steps, 20))
 
@@ -714,7 +717,9 @@ def run_native(args):
             "decomposition": f"x-slab x{world}" if world > 1 else "single block",
             **({"halo": halo_mode} if halo_mode else {}),
             **({"graph_steps": args.graph} if args.graph and world == 1 else {}),
-            "l2": "inputs larger than L2 (two population buffers of %.1f GB each)" % (vs.q * ncell * STORE_BYTES[policy] / world / 1e9),
+            **({"buffers": "one population buffer, in-place AA pattern (xlb_step_inplace)"} if args.in_place else {}),
+            "l2": "inputs larger than L2 (%s of %.1f GB%s)" % ("one population buffer" if args.in_place else "two population buffers",
+                                                                vs.q * ncell * STORE_BYTES[policy] / world / 1e9, "" if args.in_place else " each"),
         },
         "gpu_launches": int(launches),
         "finite": finite,
@@ -806,6 +811,7 @@ def main():
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS))
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--in-place", action="store_true", help="one population buffer (in-place AA pattern) instead of two; single GPU, cavity / periodic workloads")
     ap.add_argument("--e2e-steps", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-overlap", action="store_true")

@@ -145,6 +145,17 @@ int xlb_step_range(const XlbDomain* dom, int collision, const XlbCollisionParams
                    const void* f0, void* f1, const uint8_t* bc_mask, const uint8_t* missing_mask, const XlbBcEntry* bc_table, int n_bc,
                    double omega, int timestep, int variant, void* stream);
 
+/* The same step on ONE population buffer (in-place "AA" pattern; BASELINE.json north_star: "optionally the in-place AA pattern
+ * to halve memory"; no counterpart call in the reference, whose steppers are double-buffered, nse_stepper.py:227-282).
+ * parity 0 ("P" step): the buffer holds the populations in the normal layout f[l][x]; the step pulls like xlb_step and writes
+ * result m of cell x to slot opp(m) of cell x + c_m -- a location the same cell has just read, so the update is race free.
+ * parity 1 ("L" step): reads slot opp(l) of its own cell, writes slot m of its own cell: the layout is normal again.
+ * Calls must alternate 0, 1, 0, ...; after an even number of steps the buffer equals f1 of the two-buffer scheme BIT FOR BIT.
+ * Boundary conditions: none, FULLWAY and EQUILIBRIUM only (cp->bc_kind_mask must say so when n_bc > 0): the kinds that need
+ * f_pre or a neighbour need the second buffer.  Collisions: BGK, KBC, SmagorinskyLESBGK without a body force.  Whole block. */
+int xlb_step_inplace(const XlbDomain* dom, int collision, const XlbCollisionParams* cp, void* f, const uint8_t* bc_mask,
+                     const XlbBcEntry* bc_table, int n_bc, double omega, int parity, void* stream);
+
 /* Rank-to-rank ordering of the halo push, as two one-thread kernels on the caller's stream (capturable in a CUDA graph).
  * Every rank owns a monotonic 64-bit flag per side, written by that side's neighbour, and two local counters.
  *   xlb_halo_signal: ++*sent; store *sent to the two neighbours' flags (system-scope release after a system fence) -- enqueue it

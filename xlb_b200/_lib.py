@@ -95,6 +95,7 @@ EXPORTS = {
     "xlb_step": (c_int, [POINTER(XlbDomain), c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_double, c_int, c_int, c_int, c_int, c_void_p]),
     "xlb_step_ex": (c_int, [POINTER(XlbDomain), c_int, POINTER(XlbCollisionParams), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_double, c_int, c_int, c_int, c_int, c_void_p]),
     "xlb_step_range": (c_int, [POINTER(XlbDomain), c_int, POINTER(XlbCollisionParams), POINTER(XlbStepRange), POINTER(XlbHaloPush), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_double, c_int, c_int, c_void_p]),
+    "xlb_step_inplace": (c_int, [POINTER(XlbDomain), c_int, POINTER(XlbCollisionParams), c_void_p, c_void_p, c_void_p, c_int, c_double, c_int, c_void_p]),
     "xlb_halo_signal": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
     "xlb_halo_wait": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
     "xlb_ipc_export": (c_int, [c_void_p, c_void_p, POINTER(c_int64)]),

@@ -241,6 +241,61 @@ int xlb_step_range(const XlbDomain* dom, int collision, const XlbCollisionParams
     }
 }
 
+int xlb_step_inplace(const XlbDomain* dom, int collision, const XlbCollisionParams* cp, void* f, const uint8_t* bc_mask,
+                     const XlbBcEntry* bc_table, int n_bc, double omega, int parity, void* stream) {
+    if (int rc = check_domain(dom, "xlb_step_inplace")) return rc;
+    if (!f) return set_error(XLB_EINVAL, "xlb_step_inplace: null population pointer");
+    if (parity != 0 && parity != 1) return set_error(XLB_EINVAL, "xlb_step_inplace: parity must be 0 (P step) or 1 (L step)");
+    if (!dom->x_periodic && dom->d == 3) return set_error(XLB_EUNSUPPORTED, "xlb_step_inplace: single periodic block only (no ghost planes)");
+    const bool has_bc = n_bc > 0 && bc_mask && bc_table;
+    if (n_bc > 0 && !has_bc) return set_error(XLB_EINVAL, "xlb_step_inplace: n_bc > 0 needs bc_mask and bc_table");
+    if (has_bc) {
+        const int allowed = (1 << XLB_BC_NONE) | (1 << XLB_BC_FULLWAY) | (1 << XLB_BC_EQUILIBRIUM);
+        if (!cp || cp->bc_kind_mask == 0) return set_error(XLB_EINVAL, "xlb_step_inplace: cp->bc_kind_mask must list the BC kinds in bc_table");
+        if (cp->bc_kind_mask & ~allowed)
+            return set_error(XLB_EUNSUPPORTED, "xlb_step_inplace: only FullwayBounceBack and Equilibrium boundary conditions work on one buffer "
+                                               "(half-way, Zou-He, regularized, extrapolation and do-nothing read f_pre or a neighbour)");
+    }
+    if (cp && cp->has_force) return set_error(XLB_EUNSUPPORTED, "xlb_step_inplace: the body-force collisions keep the two-buffer kernels");
+    if (collision != XLB_BGK && collision != XLB_KBC && collision != XLB_SMAGORINSKY_LES_BGK)
+        return set_error(XLB_EINVAL, "xlb_step_inplace: unknown collision model");
+    StepParams p;
+    std::memset(&p, 0, sizeof(p));
+    p.f0 = f;
+    p.f1 = f;
+    p.bc_mask = has_bc ? bc_mask : nullptr;
+    p.bct = has_bc ? bc_table : nullptr;
+    p.nx = dom->nx, p.ny = dom->ny, p.nz = dom->nz;
+    p.x_begin = 0, p.x_end = dom->nx, p.x_stride = 1, p.n_planes = dom->nx;
+    p.y_begin = 0, p.y_stride = 1, p.n_rows = dom->ny;
+    p.x_periodic = 1;
+    const long long ncell = (long long)dom->nx * dom->ny * dom->nz;
+    p.qs = dom->q_stride ? dom->q_stride : ncell;
+    p.mqs = dom->mask_q_stride ? dom->mask_q_stride : ncell;
+    p.omega = omega;
+    p.bc_kind_mask = cp ? cp->bc_kind_mask : 0;
+    if (collision == XLB_SMAGORINSKY_LES_BGK) {
+        const double cs = cp ? cp->smagorinsky_coef : 0.17;
+        p.les_c = 36.0 * cs * cs;
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int key = dom->q * 100 + dom->compute_dtype * 10 + dom->store_dtype;
+    switch (key) {
+#define XLB_AA_CASE(Q, C, S, tag) \
+    case Q * 100 + C * 10 + S: return xlb_step_aa_q##Q##_##tag(collision, p, parity, st);
+#define XLB_AA_CASES(Q)                        \
+    XLB_AA_CASE(Q, XLB_F32, XLB_F32, f32f32)   \
+    XLB_AA_CASE(Q, XLB_F32, XLB_F16, f32f16)   \
+    XLB_AA_CASE(Q, XLB_F64, XLB_F64, f64f64)   \
+    XLB_AA_CASE(Q, XLB_F64, XLB_F32, f64f32)   \
+    XLB_AA_CASE(Q, XLB_F64, XLB_F16, f64f16)
+        XLB_AA_CASES(9)
+        XLB_AA_CASES(19)
+        XLB_AA_CASES(27)
+        default: return set_error(XLB_EUNSUPPORTED, "xlb_step_inplace: unsupported precision policy (precision_policy.py:57-97)");
+    }
+}
+
 // ----------------------------------------------------------------------------- halo push ordering, peer mapping, batch copies
 namespace xlb {
 __global__ void halo_signal_kernel(unsigned long long* sent, unsigned long long* left_flag, unsigned long long* right_flag) {

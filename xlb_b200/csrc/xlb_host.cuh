@@ -11,7 +11,9 @@ int count_launch(cudaError_t err);
 }  // namespace xlb
 
 // per-(lattice, policy) step entry points, defined by xlb_step_inst.cu instances
-#define XLB_DECL_STEP(tag) int xlb_step_##tag(int collision, const xlb::StepParams& p, int variant, cudaStream_t st);
+#define XLB_DECL_STEP(tag)                                                                           \
+    int xlb_step_##tag(int collision, const xlb::StepParams& p, int variant, cudaStream_t st);       \
+    int xlb_step_aa_##tag(int collision, const xlb::StepParams& p, int local_step, cudaStream_t st);
 #define XLB_FOR_ALL_POLICIES(Q)      \
     XLB_DECL_STEP(q##Q##_f32f32)     \
     XLB_DECL_STEP(q##Q##_f32f16)     \

@@ -196,9 +196,32 @@ XLB_D F2 fast_div(F2 a, F2 b) { return a * F2{make_float2(rcp_approx(b.v.x), rcp
 XLB_D float sqrt_of(float x) { return __fsqrt_rn(x); }
 XLB_D double sqrt_of(double x) { return sqrt(x); }
 XLB_D F2 sqrt_of(F2 x) { return {make_float2(__fsqrt_rn(x.v.x), __fsqrt_rn(x.v.y))}; }
+// 1 / x for the densities and relaxation times (x of order one).  XLB_TUNE_DIET_RCP: MUFU.RCP + one Newton step (two FMAs, packed
+// for F2; <= 1 ulp, no range check) instead of the IEEE-rounded __frcp_rn sequence (~8 instructions with a slow-path branch per
+// lane).  Every kernel variant goes through this function, so they stay bit-identical to each other.
+#ifndef XLB_TUNE_DIET_RCP
+#define XLB_TUNE_DIET_RCP 1
+#endif
+// BGK / LES branch experiments (profiles/r2k_sweep_diet.log: both together cost the FP16 kernel 3.7 %, the FP32 one 1.2 %):
+// bit 0 = Horner form of the equilibrium pair, bit 1 = pair-sum moments
+#ifndef XLB_TUNE_DIET_BGK
+#define XLB_TUNE_DIET_BGK 0
+#endif
+#if XLB_TUNE_DIET_RCP
+XLB_D float rcp_of(float x) {
+    const float r = rcp_approx(x);
+    return fmaf(r, fmaf(-x, r, 1.0f), r);
+}
+XLB_D F2 rcp_of(F2 x) {
+    const F2 r{make_float2(rcp_approx(x.v.x), rcp_approx(x.v.y))};
+    const F2 e = fma_(-x, r, F2{make_float2(1.0f, 1.0f)});
+    return fma_(r, e, r);
+}
+#else
 XLB_D float rcp_of(float x) { return __frcp_rn(x); }
-XLB_D double rcp_of(double x) { return 1.0 / x; }
 XLB_D F2 rcp_of(F2 x) { return {make_float2(__frcp_rn(x.v.x), __frcp_rn(x.v.y))}; }
+#endif
+XLB_D double rcp_of(double x) { return 1.0 / x; }
 // lane-wise select: flag[k] ? a : b
 XLB_D float pick(const bool* flag, float a, float b) { return flag[0] ? a : b; }
 XLB_D double pick(const bool* flag, double a, double b) { return flag[0] ? a : b; }
@@ -364,7 +387,9 @@ XLB_D void collide_cols(FS& f, const CollArgs<T>& ca, const bool* fullway, bool 
     N pi[6];  // KBC / LES: sum_l cc_l f_l, accumulated from the pair sums (cc is even in c)
 #pragma unroll
     for (int k = 0; k < 6; ++k) pi[k] = splat<N>(S(0));
-    if (MODEL != XLB_BGK) {
+    if (MODEL != XLB_BGK || (XLB_TUNE_DIET_BGK & 2)) {
+        // sums and differences of a direction and its opposite: c is odd, cc is even, so rho and the second moment take the
+        // sums, the momentum the differences (XLB_TUNE_DIET: BGK too -- 39 instead of 45 additions on D3Q19)
         static_for<Q>([&](auto lc) {
             XLB_IDX(l, lc);
             using D = Dir<Q, l>;
@@ -378,7 +403,7 @@ XLB_D void collide_cols(FS& f, const CollArgs<T>& ca, const bool* fullway, bool 
                 acc_signed<D::cx>(sx, bx, dif);
                 acc_signed<D::cy>(sy, by, dif);
                 acc_signed<D::cz>(sz, bz, dif);
-                acc_second_moment<Q, l>(pi, sum);
+                if (MODEL != XLB_BGK) acc_second_moment<Q, l>(pi, sum);
             }
         });
     } else {
@@ -435,16 +460,30 @@ XLB_D void collide_cols(FS& f, const CollArgs<T>& ca, const bool* fullway, bool 
         // out = (1-omega) f + omega feq, with omega folded into the class constants
         wclass_constants<N, S, Q>(rho, base, omega, a, ab);
         const N keep = splat<N>(S(1)) - omega;
+#if XLB_TUNE_DIET_BGK & 1
+        N ah[4];  // 0.5 a: feq_l = ab + a cu + ah cu^2 in Horner form, four FMAs per direction pair instead of five operations
+#pragma unroll
+        for (int k = 0; k < n_wclass<Q>(); ++k) ah[k] = splat<N>(S(0.5)) * a[k];
+#endif
         static_for<Q>([&](auto lc) {
             XLB_IDX(l, lc);
             constexpr int o = Dir<Q, l>::o;
             if (o == l) {
                 col_set<N>(f, l, J, fma_(keep, col_get<N>(f, l, J), ab[0]));
             } else if (o > l) {
+#if XLB_TUNE_DIET_BGK & 1
+                constexpr int k = wclass<Q, l>();
+                const N cu = cu_of<N, Q, l>(u3);
+                const N fel = fma_(cu, fma_(ah[k], cu, a[k]), ab[k]);    // w rho omega (1 - usqr + cu + cu^2 / 2)
+                const N feo = fma_(cu, fma_(ah[k], cu, -a[k]), ab[k]);   // the same with -cu
+                col_set<N>(f, l, J, fma_(keep, col_get<N>(f, l, J), fel));
+                col_set<N>(f, o, J, fma_(keep, col_get<N>(f, o, J), feo));
+#else
                 N even, odd;
                 feq_pair<N, Q, l>(u3, a, ab, even, odd);
                 col_set<N>(f, l, J, fma_(keep, col_get<N>(f, l, J), even + odd));
                 col_set<N>(f, o, J, fma_(keep, col_get<N>(f, o, J), even - odd));
+#endif
             }
         });
     } else {

@@ -7,6 +7,7 @@
 #include "xlb_step.cuh"
 #include "xlb_step_bulk.cuh"
 #include "xlb_step_h2.cuh"
+#include "xlb_step_aa.cuh"
 
 #ifndef XLB_Q
 #error "compile with -DXLB_Q -DXLB_TC -DXLB_TS -DXLB_TAG"
@@ -247,6 +248,44 @@ static int step_main(const StepParams& p, int variant, cudaStream_t st) {
     return has_bc ? launch_vector<T, S, Q, COLL, 1, true>(p, st) : launch_vector<T, S, Q, COLL, 1, false>(p, st);
 }
 
+// ---- in-place (AA) step, xlb_step_aa.cuh: P step (local_step == 0) or L step
+template <typename T, typename S, int Q, int COLL, int V, bool HAS_BC, bool LOCAL>
+static int launch_aa(const StepParams& p0, cudaStream_t st) {
+    constexpr int BLOCK = 128;
+#ifdef XLB_TUNE_AA_MINB
+    constexpr int MINB = XLB_TUNE_AA_MINB;
+#else
+    constexpr int MINB = (V == 1) ? 4 : default_minb<S, Q, V>();
+#endif
+    StepParams p = p0;
+    p.ntz = p.nz / V;
+    p.ntz_shift = -1;
+    for (int b = 0; b < 31; ++b)
+        if ((1 << b) == p.ntz) p.ntz_shift = b;
+    const long long nvec = (long long)p.n_rows * p.ntz;
+    dim3 grid((unsigned)((nvec + BLOCK - 1) / BLOCK), (unsigned)p.n_planes, 1);
+    step_aa_kernel<T, S, Q, COLL, V, BLOCK, MINB, HAS_BC, LOCAL><<<grid, BLOCK, 0, st>>>(p);
+    return count_launch(cudaGetLastError());
+}
+
+template <typename T, typename S, int Q, int COLL>
+static int step_aa(const StepParams& p, int local_step, cudaStream_t st) {
+    // FP16 storage: 4 cells per thread here (the 8-cell packed-half2 layout belongs to the two-buffer kernel)
+    constexpr int VMAX = (sizeof(S) == 2) ? 4 : default_vec<T, S, Q>();
+    const bool has_bc = p.bc_mask != nullptr && p.bct != nullptr;
+    const uintptr_t a = reinterpret_cast<uintptr_t>(p.f1);
+    const bool vec_ok = (p.nz % VMAX == 0) && (p.qs % VMAX == 0) && (a % (VMAX * sizeof(S)) == 0) &&
+                        (!has_bc || reinterpret_cast<uintptr_t>(p.bc_mask) % VMAX == 0);
+#define XLB_AA_GO(V)                                                                                                        \
+    do {                                                                                                                    \
+        if (has_bc) return local_step ? launch_aa<T, S, Q, COLL, V, true, true>(p, st) : launch_aa<T, S, Q, COLL, V, true, false>(p, st);  \
+        return local_step ? launch_aa<T, S, Q, COLL, V, false, true>(p, st) : launch_aa<T, S, Q, COLL, V, false, false>(p, st);            \
+    } while (0)
+    if (vec_ok) XLB_AA_GO(VMAX);
+    XLB_AA_GO(1);
+#undef XLB_AA_GO
+}
+
 }  // namespace xlb
 
 #define XLB_CAT2(a, b) a##b
@@ -271,5 +310,23 @@ int XLB_CAT(xlb_step_, XLB_TAG)(int collision, const xlb::StepParams& p, int var
         default: break;
     }
     return set_error(XLB_EUNSUPPORTED, "xlb_step: collision model not supported for this velocity set (KBC needs D2Q9 or D3Q27; kbc.py:65-66)");
+#endif
+}
+
+int XLB_CAT(xlb_step_aa_, XLB_TAG)(int collision, const xlb::StepParams& p, int local_step, cudaStream_t st) {
+    using namespace xlb;
+#ifdef XLB_STUB
+    (void)collision; (void)p; (void)local_step; (void)st;
+    return set_error(XLB_EUNSUPPORTED, "xlb_step_inplace: this (lattice, policy) instance was stubbed out of a tuning build");
+#else
+    switch (collision) {  // the body-force variants read their own output between two passes; they keep the two-buffer kernels
+        case XLB_BGK: return step_aa<XLB_TC, XLB_TS, XLB_Q, XLB_BGK>(p, local_step, st);
+        case XLB_SMAGORINSKY_LES_BGK: return step_aa<XLB_TC, XLB_TS, XLB_Q, XLB_SMAGORINSKY_LES_BGK>(p, local_step, st);
+#if XLB_Q != 19
+        case XLB_KBC: return step_aa<XLB_TC, XLB_TS, XLB_Q, XLB_KBC>(p, local_step, st);
+#endif
+        default: break;
+    }
+    return set_error(XLB_EUNSUPPORTED, "xlb_step_inplace: BGK, KBC (D2Q9 / D3Q27) and SmagorinskyLESBGK without a body force");
 #endif
 }

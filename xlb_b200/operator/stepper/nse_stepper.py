@@ -55,6 +55,22 @@ class IncompressibleNavierStokesStepper(Stepper):
         self._collision_params = self.collision.abi_params() or _lib.XlbCollisionParams()
         for bc in self.boundary_conditions:  # which BC kinds the kernel has to be able to handle (0 would mean "any")
             self._collision_params.bc_kind_mask |= 1 << int(bc.abi_kind)
+        # backend_config["in_place"]: one population buffer instead of two (the in-place AA pattern, csrc/xlb_step_aa.cuh):
+        # prepare_fields() returns the SAME tensor as f_0 and f_1, the usual loop ``f_0, f_1 = stepper(f_0, f_1, ...); swap``
+        # runs unchanged, and after every even number of steps the buffer holds exactly what f_0 would hold in the two-buffer
+        # scheme (after an odd number it is in the pattern's intermediate layout: read results on even step counts).
+        self.in_place = bool(self.backend_config.get("in_place", False)) if self.backend_config else False
+        self.aa_parity = 0  # 0: the next in-place step is a P step (buffer in the normal layout), 1: an L step
+        if self.in_place:
+            bad = [bc.__class__.__name__ for bc in self.boundary_conditions if int(bc.abi_kind) not in (_lib.BC_FULLWAY, _lib.BC_EQUILIBRIUM)]
+            if bad:
+                raise NotImplementedError(
+                    f"in_place stepping supports FullwayBounceBackBC and EquilibriumBC only; {sorted(set(bad))} read f_pre or a "
+                    "neighbour cell and need the second buffer")
+            if force_vector is not None:
+                raise NotImplementedError("in_place stepping: the body-force collisions keep the two-buffer kernels")
+            if getattr(grid, "halo", 0):
+                raise NotImplementedError("in_place stepping runs on a single block (no slab decomposition)")
         self.streaming_scheme = streaming_scheme
         if streaming_scheme != "pull":
             raise NotImplementedError(f"Unknown or unimplemented streaming scheme for backend: {self.compute_backend}")  # nse_stepper.py:91-92
@@ -76,9 +92,18 @@ class IncompressibleNavierStokesStepper(Stepper):
 
     # ------------------------------------------------------------------ setup (nse_stepper.py:99-205)
     def prepare_fields(self, initializer=None):
-        _, f_0, f_1, missing_mask, bc_mask = create_nse_fields(
-            grid=self.grid, velocity_set=self.velocity_set, compute_backend=self.compute_backend, precision_policy=self.precision_policy
-        )
+        if self.in_place:  # one population buffer: never allocate the second one, not even transiently
+            from ...precision_policy import Precision
+
+            f_0 = self.grid.create_field(cardinality=self.velocity_set.q, dtype=self.precision_policy.store_precision)
+            f_1 = f_0
+            missing_mask = self.grid.create_field(cardinality=self.velocity_set.q, dtype=Precision.BOOL)
+            bc_mask = self.grid.create_field(cardinality=1, dtype=Precision.UINT8)
+            self.aa_parity = 0
+        else:
+            _, f_0, f_1, missing_mask, bc_mask = create_nse_fields(
+                grid=self.grid, velocity_set=self.velocity_set, compute_backend=self.compute_backend, precision_policy=self.precision_policy
+            )
         self._collision_params.halfway_fraction = self._halfway_fraction(bc_mask)
         bc_mask, missing_mask = self._process_boundary_conditions(self.boundary_conditions, bc_mask, missing_mask)
         if initializer is not None:
@@ -93,10 +118,10 @@ class IncompressibleNavierStokesStepper(Stepper):
                     f_0[l].fill_(float(w[l]))
             else:
                 f_0 = initialize_eq(f_0, self.grid, self.velocity_set, self.precision_policy, self.compute_backend)
-        if self.boundary_conditions:
+        if self.boundary_conditions and not self.in_place:
             self._bc_cell_list(f_0, bc_mask)  # built here so that the step loop itself never synchronises
             self._missing_bits(f_0, missing_mask)
-        return f_0, f_1, bc_mask, missing_mask
+        return f_0, (f_0 if self.in_place else f_1), bc_mask, missing_mask
 
     def _halfway_fraction(self, bc_mask):
         """Share of this block's cells listed by HalfwayBounceBackBC objects (obstacle interiors included): a hint for the
@@ -298,7 +323,28 @@ class IncompressibleNavierStokesStepper(Stepper):
             return _lib.XlbStepRange(0, 1, 1, halo, 1, int(dom.ny) - 2 * halo)
         return _lib.XlbStepRange(int(x_begin), 1, int(x_end) - int(x_begin), 0, 1, 0)
 
+    def launch_in_place(self, f, bc_mask, omega):
+        """One ``xlb_step_inplace`` launch on the single buffer ``f``; alternates P and L steps (``aa_parity``)."""
+        q = self.velocity_set.q
+        if f.dtype != self.store_dtype:
+            raise ValueError(f"populations must be stored as {self.store_dtype} under policy {self.precision_policy.name}")
+        self._check_field(f, "f", q)
+        _, dom, table, n_bc, _, _ = self._get_plan(f)
+        if n_bc:
+            self._check_field(bc_mask, "bc_mask", 1)
+        rc = lib().xlb_step_inplace(
+            byref(dom), self.collision.abi_model, byref(self._collision_params), f.data_ptr(), bc_mask.data_ptr() if n_bc else None,
+            table.data_ptr() if n_bc else None, n_bc, float(omega), int(self.aa_parity), stream_ptr(),
+        )
+        check(rc, "IncompressibleNavierStokesStepper")
+        self.aa_parity ^= 1
+
     @Operator.register_backend(ComputeBackend.CUDA)
     def cuda_implementation(self, f_0, f_1, bc_mask, missing_mask, omega, timestep):
+        if self.in_place:
+            if f_0.data_ptr() != f_1.data_ptr():
+                raise ValueError("this stepper was built with in_place=True: pass the one buffer prepare_fields() returned as f_0 and f_1")
+            self.launch_in_place(f_0, bc_mask, omega)
+            return f_0, f_1
         self.launch(f_0, f_1, bc_mask, missing_mask, omega, timestep)
         return f_0, f_1

@@ -1,7 +1,8 @@
 """Lattice velocity sets (xlb/velocity_set/velocity_set.py:20-253).
 
 Host-side constants only: the kernels carry their own compile-time copies of the same tables
-(csrc/xlb_common.cuh); ``tests/test_velocity_sets.py`` checks both against each other's ordering.
+(csrc/xlb_common.cuh); ``tests/test_host_logic.py::test_velocity_set_matches_oracle`` checks these against the oracle's tables and
+the stream / step parity tests (``tests/test_gpu_operators.py``, ``tests/test_gpu_step.py``) check the kernels' copies through their results.
 Attributes keep the reference's names: ``c`` (d, q) int, ``w`` (q,), ``opp_indices``, ``cc``, ``qi``,
 ``main_indices``, ``right_indices``, ``left_indices``, ``center_index``, ``cs``, ``cs2``, ``inv_cs2``.
 """
