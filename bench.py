@@ -196,6 +196,27 @@ def build_case(workload, slab=None, shape=None, variant=0, radius=None, backend_
     return stepper, vs, pol, shape, omega
 
 
+# relative cost of a cell of a large half-way obstacle (all solid cells are tagged; they take the half-way path of the fused kernel):
+# a 192 x 1536 x 1536 block that holds half of the r = 192 sphere (3.3 % of its cells) runs 18 % slower than one without
+# (profiles/r2i_bigsphere.log vs r2m_bench_default.json) -> 1 + 0.18 / 0.033
+HALFWAY_CELL_COST = 6.5
+
+
+def obstacle_plane_cost(kind, shape, radius=None):
+    """Relative cost of every global x plane of a sphere / wind-tunnel workload (same geometry as build_case)."""
+    import numpy as np
+
+    nx, ny, nz = shape
+    r, cx = ny // 12, nx // 6
+    if kind == "windtunnel":
+        r, cx = min(ny // 8, nx // 4), nx // 3
+    if radius is not None:
+        r = int(radius)
+    t = np.arange(nx) - cx
+    solid = np.pi * np.clip(r * r - t * t, 0, None)  # cells of the sphere's cross-section in plane x
+    return ny * nz + (HALFWAY_CELL_COST - 1.0) * solid
+
+
 # --------------------------------------------------------------------------- CPU legs (the only users of oracle/)
 def host_threads():
     """Host threads this process may use (torchrun exports OMP_NUM_THREADS=1, which is not the box's core count)."""
@@ -524,7 +545,15 @@ def run_native(args):
         shape = tuple(shape) if shape else shape0
         if world > 1 and not strong:
             shape = (shape[0] * world,) + tuple(shape[1:])  # weak scaling: the N=1 block per GPU, stacked along x
-        stepper, vs, pol, shape, omega = build_case(workload, slab=slab, shape=shape, variant=args.variant, radius=args.radius,
+        run_slab = slab
+        planes = None
+        if slab is not None and kind != "cavity" and not args.no_balance:
+            # obstacle workloads: slabs of equal COST, not of equal plane count (every rank waits for the slowest one each step)
+            from xlb_b200.distribute import SlabDecomposition, balanced_planes
+
+            planes = balanced_planes(obstacle_plane_cost(kind, shape, args.radius), world)
+            run_slab = SlabDecomposition(rank=rank, world=world, planes=planes)
+        stepper, vs, pol, shape, omega = build_case(workload, slab=run_slab, shape=shape, variant=args.variant, radius=args.radius,
                                                     backend_config={"in_place": True} if args.in_place else None)
         if slab is not None:
             from xlb_b200.distribute import distribute
@@ -538,7 +567,7 @@ def run_native(args):
             t += 1
         barrier()
         return dict(stepper=stepper, vs=vs, policy=policy, shape=shape, omega=omega, fields=(f_0, f_1, bc_mask, missing), t=t,
-                    lattice=lattice, collision=collision, ncell=shape[0] * shape[1] * shape[2])
+                    lattice=lattice, collision=collision, ncell=shape[0] * shape[1] * shape[2], planes=planes)
 
     workload = args.workload
     shape_arg = tuple(int(v) for v in args.shape.split(",")) if args.shape else None
@@ -715,6 +744,8 @@ def run_native(args):
         "config": {
             "workload": workload, "lattice": lattice, "collision": collision, "policy": policy, "shape": list(shape), "omega": omega,
             "decomposition": f"x-slab x{world}" if world > 1 else "single block",
+            **({"slab_planes": run["planes"], "slab_balance": "planes per rank from a per-plane cost: cells + %.1f x half-way obstacle cells" % (HALFWAY_CELL_COST - 1.0)}
+               if run.get("planes") else {}),
             **({"halo": halo_mode} if halo_mode else {}),
             **({"graph_steps": args.graph} if args.graph and world == 1 else {}),
             **({"buffers": "one population buffer, in-place AA pattern (xlb_step_inplace)"} if args.in_place else {}),
@@ -815,6 +846,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-overlap", action="store_true")
+    ap.add_argument("--no-balance", action="store_true", help="N>1, obstacle workloads: equal plane counts per rank instead of equal cost")
     ap.add_argument("--halo", default="auto", choices=["auto", "peer", "nccl"], help="N>1: halo exchange fused into the edge launch over peer memory, or NCCL send/recv")
     ap.add_argument("--no-dist-graph", action="store_true", help="N>1: issue the distributed step eagerly instead of replaying its CUDA graph")
     ap.add_argument("--no-configs", action="store_true", help="skip the extra BASELINE configs block (N=1) / the bitwise check and the strong-scaling line (N>1)")

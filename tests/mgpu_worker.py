@@ -34,10 +34,23 @@ def main():
         (cases.cavity2d(0, shape=(8 * world + 1, 24), omega=1.6), 25),
         (cases.cavity2d(0, shape=(6 * world, 32), collision="KBC", policy="FP64FP64", omega=1.7), 10),
     ]
+
+    def uneven(nx):
+        """Plane counts that differ by 4 between neighbours (what a cost-balanced decomposition hands out, balanced_planes)."""
+        planes = [nx // world] * world
+        planes[0] += nx - sum(planes)
+        for r in range(0, world - 1, 2):
+            planes[r] += 2
+            planes[r + 1] -= 2
+        return planes
+
+    sphere = cases.sphere3d((12 * world if world > 2 else 36, 24, 24), lattice="D3Q27", collision="KBC", omega=1.7)
+    todo.append((sphere, 10, uneven(sphere["shape"][0])))
     # (halo exchange, overlap schedule, CUDA-graph replay): the fused peer push (default), the same serialised and eager,
     # and the NCCL send/recv schedule
     modes = [("peer", True, True), ("peer", False, False), ("nccl", True, False)]
-    for case, nsteps in todo:
+    for case, nsteps, *rest in todo:
+        planes = rest[0] if rest else None
         for halo, overlap, graph in modes:
             # single-GPU reference of the global problem, on every rank
             st, _ = build_product(case)
@@ -48,7 +61,7 @@ def main():
                 f_0, f_1 = f_1, f_0
             ref, ref_bc, ref_mm = f_0.clone(), bc_mask.clone(), missing.clone()
             # distributed run
-            dec = SlabDecomposition()
+            dec = SlabDecomposition(planes=planes)
             # with the overlap schedule the slab stepper also runs the BC-cell-list path (forced: these blocks are far
             # below the size where "auto" would pick it), so its per-plane slicing is covered by the bitwise comparison
             st, _ = build_product(case, backend_config={"bc_cell_list": True} if overlap else None, decomposition=dec)
@@ -89,7 +102,7 @@ def main():
                 assert err < 1e-6, f"rank {rank}: MomentumTransfer distributed {f_dist.tolist()} != single {f_ref.tolist()}"
             dst.close()
             if rank == 0:
-                print(f"OK {case['name']} world={world} halo={halo} overlap={overlap} graph={graph} steps={nsteps}: bitwise equal to the single-GPU run", flush=True)
+                print(f"OK {case['name']} world={world} halo={halo} overlap={overlap} graph={graph} planes={planes or 'even'} steps={nsteps}: bitwise equal to the single-GPU run", flush=True)
     dist.barrier()
     dist.destroy_process_group()
 

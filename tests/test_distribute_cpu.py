@@ -21,7 +21,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, lattice, shape, out_dir):
+def _worker(rank, world, port, lattice, shape, out_dir, planes=None):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -31,9 +31,11 @@ def _worker(rank, world, port, lattice, shape, out_dir):
         lat = make_lattice(lattice)
         rng = np.random.default_rng(7)
         f = rng.uniform(0, 1, (lat.q,) + shape).astype(np.float32)
-        dec = SlabDecomposition()
+        dec = SlabDecomposition(planes=planes)
         assert (dec.rank, dec.world) == (rank, world)
         x0, n = dec.local_range(shape[0])
+        if planes is not None:
+            assert n == planes[rank] and x0 == sum(planes[:rank])
         slab = np.full((lat.q, n + 2) + shape[1:], np.nan, np.float32)
         slab[:, 1:-1] = f[:, x0 : x0 + n]
         t = torch.from_numpy(slab)
@@ -62,6 +64,43 @@ def _worker(rank, world, port, lattice, shape, out_dir):
 def test_halo_ring_gloo(world, lattice, shape, tmp_path):
     mp.spawn(_worker, args=(world, _free_port(), lattice, shape, str(tmp_path)), nprocs=world, join=True)
     assert all((tmp_path / f"ok{r}").exists() for r in range(world))
+
+
+def test_halo_ring_gloo_with_given_planes(tmp_path):
+    """Slabs of unequal plane counts (cost-balanced decomposition): same ring, same result."""
+    world, planes = 3, [5, 2, 4]
+    mp.spawn(_worker, args=(world, _free_port(), "D3Q19", (11, 4, 3), str(tmp_path), planes), nprocs=world, join=True)
+    assert all((tmp_path / f"ok{r}").exists() for r in range(world))
+
+
+def test_balanced_planes():
+    from xlb_b200.distribute import SlabDecomposition, balanced_planes
+
+    assert balanced_planes(np.ones(16), 8) == [2] * 8
+    assert sum(balanced_planes(np.ones(17), 8)) == 17 and min(balanced_planes(np.ones(17), 8)) >= 2
+    # an expensive region in the middle: the ranks that hold it get fewer planes, every share is within one plane's cost of even
+    cost = np.ones(96)
+    cost[40:56] = 4.0
+    planes = balanced_planes(cost, 4)
+    assert sum(planes) == 96 and min(planes) >= 2
+    cuts = np.cumsum([0] + planes)
+    shares = [cost[cuts[r] : cuts[r + 1]].sum() for r in range(4)]
+    assert max(shares) - min(shares) <= 2 * cost.max() and max(shares) < 1.1 * cost.sum() / 4
+    assert max(planes) > 96 // 4 > min(planes)
+    # a cost so concentrated that the even-cost cut would leave a rank without planes: the minimum is kept
+    spike = np.ones(12)
+    spike[0] = 1000.0
+    p = balanced_planes(spike, 4)
+    assert sum(p) == 12 and min(p) >= 2
+    with pytest.raises(ValueError):
+        balanced_planes(np.ones(7), 4)
+    # the decomposition takes the list as it is, and checks it against nx
+    dec = SlabDecomposition(1, 4, planes=planes)
+    assert dec.local_range(96) == (planes[0], planes[1])
+    with pytest.raises(ValueError):
+        dec.local_range(97)
+    with pytest.raises(ValueError):
+        SlabDecomposition(0, 2, planes=[1, 7]).local_range(8)
 
 
 def _worker_2d(rank, world, port, shape, out_dir):

@@ -27,7 +27,7 @@ def test_slab_run_equals_single_gpu(world):
            "--master-port", str(_free_port()), os.path.join(ROOT, "tests", "mgpu_worker.py")]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=ROOT)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
-    assert r.stdout.count("OK ") == 21, r.stdout
+    assert r.stdout.count("OK ") == 24, r.stdout
 
 
 @pytest.mark.parametrize("world", [2, 4])

@@ -37,7 +37,7 @@ def run(workload, steps, only="", variant=0, shape=None):
     for lib in sorted(glob.glob(os.path.join(SWEEP_DIR, f"lib_{only}*.so"))):
         env = dict(os.environ, XLB_B200_LIB=lib, XLB_B200_TUNING_LIB="1")
         r = subprocess.run(
-            [sys.executable, os.path.join(ROOT, "bench.py"), "--workload", workload, "--steps", str(steps), "--warmup", "3", "--no-e2e", "--no-cpu-baseline", "--variant", str(variant)] + (["--shape", shape] if shape else []),
+            [sys.executable, os.path.join(ROOT, "bench.py"), "--workload", workload, "--steps", str(steps), "--warmup", "3", "--no-e2e", "--no-cpu-baseline", "--variant", str(variant)] + (["--shape", shape] if shape else []) + os.environ.get("XLB_SWEEP_BENCH_ARGS", "").split(),
             env=env, capture_output=True, text=True,
         )
         line = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]

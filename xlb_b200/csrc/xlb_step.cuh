@@ -195,6 +195,10 @@ XLB_D __half ld_if(const __half* ptr, bool pred, __half keep) {
 // fast path of this kernel is register-critical: compiling the extra path into the BC-free / cavity instance costs 5-8 %.
 // PUSH: the halo-push instance (XlbHaloPush) -- used for the edge-plane launch of a slab only; the instance that updates the
 // bulk of the lattice is compiled without it, because even three more live registers in the store loop cost it spills.
+#ifndef XLB_TUNE_K1_PHASED
+#define XLB_TUNE_K1_PHASED 0  // 1: ids -> all population loads -> classification -> shifts
+#endif
+
 template <typename T, typename S, int Q, int COLL, int V, int BLOCK, int MINB, bool HAS_BC, bool HALF = false, bool PUSH = false>
 __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_constant__ StepParams p) {
     const S* __restrict__ f0 = static_cast<const S*>(p.f0);
@@ -224,11 +228,12 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_c
     bool k_full[V], k_eq[V], k_half[V];
 #pragma unroll
     for (int j = 0; j < V; ++j) k_full[j] = k_eq[j] = k_half[j] = false;
-    if (HAS_BC) {
-        const Vec<uint8_t, V> w = ld_vec<uint8_t, V>(p.bc_mask + cell);
+    Vec<uint8_t, V> idv;
+    if (HAS_BC) idv = ld_vec<uint8_t, V>(p.bc_mask + cell);
+    auto classify = [&]() {
 #pragma unroll
         for (int j = 0; j < V; ++j) {
-            ids[j] = w.v[j];
+            ids[j] = idv.v[j];
             any_bc |= ids[j] != 0;
         }
         if (any_bc) {
@@ -250,7 +255,10 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_c
                 }
             }
         }
-    }
+    };
+#if !XLB_TUNE_K1_PHASED
+    if (HAS_BC) classify();
+#endif
 
     // ---- pull-stream: one aligned vector load per population
     const int xm = p.x_periodic ? wrap1(x - 1, p.nx) : x - 1;
@@ -265,6 +273,48 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_c
     const int z_hi = (tz == p.ntz - 1) ? 0 : z0 + V;  // source of the element right of my vector
     T f[Q][V];
     const S* pl = f0;
+#if XLB_TUNE_K1_PHASED
+    // phase 1: issue every population's vector load before anything waits on one.  With the classification of tagged cells in
+    // front of the loads, and the exit of inactive lanes between the z-shifted populations and the rest, a thread made three
+    // dependent round trips to DRAM (ids -> shifted populations -> the others; ncu source page)
+    Vec<S, V> vv[Q];
+    static_for<Q>([&](auto lc) {
+        XLB_IDX(l, lc);
+        using D = Dir<Q, l>;
+        const long long ox = D::cx == 0 ? ox0 : (D::cx == 1 ? oxm : oxp);
+        const int oy = D::cy == 0 ? oy0 : (D::cy == 1 ? oym : oyp);
+        vv[l] = ld_vec<S, V>(pl + (ox + oy) + z0);
+        pl += p.qs;
+    });
+    if (HAS_BC) classify();
+    // phase 2: the z shift (neighbour lanes by shuffle, across the warp boundary by a predicated scalar load)
+    pl = f0;
+    static_for<Q>([&](auto lc) {
+        XLB_IDX(l, lc);
+        using D = Dir<Q, l>;
+        const Vec<S, V>& v = vv[l];
+        if (D::cz == 0) {
+#pragma unroll
+            for (int j = 0; j < V; ++j) f[l][j] = to_compute<T, S>(v.v[j]);
+        } else {
+            const long long ox = D::cx == 0 ? ox0 : (D::cx == 1 ? oxm : oxp);
+            const int oy = D::cy == 0 ? oy0 : (D::cy == 1 ? oym : oyp);
+            const S* row = pl + (ox + oy);
+            if (D::cz == 1) {  // pull from z-1
+                const S left = ld_if(row + z_lo, edge_lo, shfl_up1(v.v[V - 1]));
+                f[l][0] = to_compute<T, S>(left);
+#pragma unroll
+                for (int j = 1; j < V; ++j) f[l][j] = to_compute<T, S>(v.v[j - 1]);
+            } else {  // pull from z+1
+                const S right = ld_if(row + z_hi, edge_hi, shfl_down1(v.v[0]));
+#pragma unroll
+                for (int j = 0; j < V - 1; ++j) f[l][j] = to_compute<T, S>(v.v[j + 1]);
+                f[l][V - 1] = to_compute<T, S>(right);
+            }
+        }
+        pl += p.qs;
+    });
+#else
     static_for<Q>([&](auto lc) {
         XLB_IDX(l, lc);
         using D = Dir<Q, l>;
@@ -288,6 +338,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_c
         }
         pl += p.qs;
     });
+#endif
     if (!active) return;
 
     if (HAS_BC && slow) {

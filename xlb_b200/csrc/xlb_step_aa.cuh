@@ -52,28 +52,13 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_aa_kernel(const __grid_const
     const long long plane = (long long)p.ny * p.nz;
     const long long cell = x * plane + (long long)y * p.nz + z0;
 
-    // BC state kept packed (one id word, two bit masks) so that it costs three registers across the loads, not 3 * V
-    uint32_t idw = 0, full_mask = 0, eq_mask = 0;
-    if (HAS_BC) {
-        const Vec<uint8_t, V> w = ld_vec<uint8_t, V>(p.bc_mask + cell);
+    // BC state kept packed (two bit masks) so that it costs two registers across the collision, not 2 * V.  The ids are LOADED
+    // here and first LOOKED AT after every population load has been issued: a branch on them up here would put one full DRAM
+    // round trip in front of the loads (ncu source page of the FP16 kernel).
+    Vec<uint8_t, V> idv;
 #pragma unroll
-        for (int j = 0; j < V; ++j) idw |= (uint32_t)w.v[j] << (8 * (j & 3)) * (V <= 4);
-        if (V > 4) {  // V = 8 (FP16): ids do not fit one word; the masks are what the rest of the kernel needs
-#pragma unroll
-            for (int j = 0; j < V; ++j) idw |= w.v[j];
-        }
-        if (idw) {
-#pragma unroll
-            for (int j = 0; j < V; ++j) {
-                if (w.v[j]) {
-                    const int k = p.bct[w.v[j]].kind;
-                    full_mask |= (uint32_t)(k == XLB_BC_FULLWAY) << j;
-                    eq_mask |= (uint32_t)(k == XLB_BC_EQUILIBRIUM) << j;
-                }
-            }
-        }
-    }
-    const bool any_bc = idw != 0;
+    for (int j = 0; j < V; ++j) idv.v[j] = 0;
+    if (HAS_BC) idv = ld_vec<uint8_t, V>(p.bc_mask + cell);
 
     // row offsets of the P step's neighbour accesses, indexed by c (0 -> same, +1 -> minus side, -1 -> plus side).  They are
     // needed before AND after the collision; holding them across it costs ~14 registers the collision has to spill for, so the
@@ -131,13 +116,28 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_aa_kernel(const __grid_const
     });
     // inactive lanes only served the load shuffles; they stay alive for the store shuffles of the P step as well
 
+    uint32_t full_mask = 0, eq_mask = 0;
+    if (HAS_BC) {
+        bool any = false;
+#pragma unroll
+        for (int j = 0; j < V; ++j) any |= idv.v[j] != 0;
+        if (any) {
+#pragma unroll
+            for (int j = 0; j < V; ++j) {
+                if (idv.v[j]) {
+                    const int k = p.bct[idv.v[j]].kind;
+                    full_mask |= (uint32_t)(k == XLB_BC_FULLWAY) << j;
+                    eq_mask |= (uint32_t)(k == XLB_BC_EQUILIBRIUM) << j;
+                }
+            }
+        }
+    }
     if (HAS_BC && eq_mask) {
-        // EquilibriumBC (STREAMING step): feq(rho_bc, u_bc) constants.  The id is re-read from bc_mask (an L1 / L2 hit on this
-        // rare path) rather than held in registers since the top of the kernel.
+        // EquilibriumBC (STREAMING step): feq(rho_bc, u_bc) constants
 #pragma unroll
         for (int j = 0; j < V; ++j) {
             if ((eq_mask >> j) & 1) {
-                const double* tab = p.bct[p.bc_mask[cell + j]].table;
+                const double* tab = p.bct[idv.v[j]].table;
 #pragma unroll
                 for (int l = 0; l < Q; ++l) f[l][j] = static_cast<T>(tab[l]);
             }

@@ -74,6 +74,10 @@ XLB_D void st_words(void* p, const uint32_t (&w)[W]) {
     }
 }
 
+#ifndef XLB_TUNE_H2_PHASED
+#define XLB_TUNE_H2_PHASED 1  // 1: ids -> all population loads -> classification -> shifts (one DRAM round trip instead of three)
+#endif
+
 template <int Q, int COLL, int V, int BLOCK, int MINB, bool HAS_BC, bool HALF, bool PUSH = false>
 __global__ void __launch_bounds__(BLOCK, MINB) step_vector_h2_kernel(const __grid_constant__ StepParams p) {
     using T = float;
@@ -119,6 +123,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_h2_kernel(const __gri
             idw[0] = t.x;
             idw[1] = t.y;
         }
+    }
+    auto classify = [&]() {
 #pragma unroll
         for (int k = 0; k < (V + 3) / 4; ++k) any_bc |= idw[k] != 0;
         if (any_bc) {
@@ -145,7 +151,10 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_h2_kernel(const __gri
                 }
             }
         }
-    }
+    };
+#if !XLB_TUNE_H2_PHASED
+    if (HAS_BC) classify();
+#endif
 
     // ---- pull-stream: one aligned vector load per population, kept packed; the z shift is a byte permute
     const int xm = p.x_periodic ? wrap1(x - 1, p.nx) : x - 1;
@@ -172,6 +181,57 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_h2_kernel(const __gri
     }
     long long poff = 0;  // l * q_stride: the same for every thread of the grid (uniform datapath)
 #endif
+#if XLB_TUNE_H2_PHASED
+    // phase 1: issue every population's vector load before anything waits on one (the classification of tagged cells, the
+    // shuffles and the exit of inactive lanes used to split the loads into three dependent round trips to DRAM: ids -> the
+    // z-shifted populations -> the others; ncu source page, profiles/r2g_ncu_details_f16.txt)
+    Words<W> vv[Q];
+    static_for<Q>([&](auto lc) {
+        XLB_IDX(l, lc);
+        using D = Dir<Q, l>;
+#if XLB_TUNE_H2_ROWPTR
+        const S* row = rowp[D::cx == 0 ? 0 : (D::cx == 1 ? 1 : 2)][D::cy == 0 ? 0 : (D::cy == 1 ? 1 : 2)] + poff;
+        poff += p.qs;
+#else
+        const long long ox = D::cx == 0 ? ox0 : (D::cx == 1 ? oxm : oxp);
+        const int oy = D::cy == 0 ? oy0 : (D::cy == 1 ? oym : oyp);
+        const S* row = pl + (ox + oy);
+#endif
+        vv[l] = ld_words<W>(row + z0);
+        pl += p.qs;
+    });
+    if (HAS_BC) classify();
+    // phase 2: the z shift (a byte permute; the element across the lane boundary comes by shuffle, across the warp boundary by
+    // a predicated scalar load)
+    pl = f0;
+    static_for<Q>([&](auto lc) {
+        XLB_IDX(l, lc);
+        using D = Dir<Q, l>;
+        const Words<W>& v = vv[l];
+        if (D::cz == 0) {
+#pragma unroll
+            for (int k = 0; k < W; ++k) raw[l][k] = v.w[k];
+        } else {
+            const long long ox = D::cx == 0 ? ox0 : (D::cx == 1 ? oxm : oxp);
+            const int oy = D::cy == 0 ? oy0 : (D::cy == 1 ? oym : oyp);
+            const S* row = pl + (ox + oy);
+            if (D::cz == 1) {  // pull from z-1: cell j takes element j-1; element -1 comes from the lane to the left
+                const uint32_t prev = __shfl_up_sync(0xffffffffu, v.w[W - 1], 1);
+                const uint32_t left = ld_if_u16(row + z_lo, edge_lo, prev >> 16);
+                raw[l][0] = __byte_perm(left, v.w[0], 0x5410);
+#pragma unroll
+                for (int k = 1; k < W; ++k) raw[l][k] = __byte_perm(v.w[k - 1], v.w[k], 0x5432);
+            } else {  // pull from z+1: cell j takes element j+1; element V comes from the lane to the right
+                const uint32_t next = __shfl_down_sync(0xffffffffu, v.w[0], 1);
+                const uint32_t right = ld_if_u16(row + z_hi, edge_hi, next & 0xffffu);
+#pragma unroll
+                for (int k = 0; k < W - 1; ++k) raw[l][k] = __byte_perm(v.w[k], v.w[k + 1], 0x5432);
+                raw[l][W - 1] = __byte_perm(v.w[W - 1], right, 0x5432);
+            }
+        }
+        pl += p.qs;
+    });
+#else
     static_for<Q>([&](auto lc) {
         XLB_IDX(l, lc);
         using D = Dir<Q, l>;
@@ -202,6 +262,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_h2_kernel(const __gri
         }
         pl += p.qs;
     });
+#endif
     if (!active) return;
 
     if (HAS_BC && slow) {

@@ -31,6 +31,7 @@ rank 0): global streaming is periodic, walls are boundary conditions.
 
 import ctypes
 
+import numpy as np
 import torch
 import torch.distributed as dist
 
@@ -42,8 +43,12 @@ from ..default_config import DefaultConfig
 class SlabDecomposition:
     """Which x planes a rank owns, and who its ring neighbours are."""
 
-    def __init__(self, rank=None, world=None, group=None):
+    def __init__(self, rank=None, world=None, group=None, planes=None):
+        """``planes``: owned x planes per rank (a list of ``world`` counts summing to nx) instead of the even split -- for
+        domains whose cost per plane is not uniform (a large obstacle makes the planes it crosses dearer: every rank waits for
+        the slowest one each step); ``balanced_planes`` derives such a list from a per-plane cost."""
         self.group = group
+        self.planes = None if planes is None else [int(n) for n in planes]
         if world is None:
             world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
         if rank is None:
@@ -58,6 +63,13 @@ class SlabDecomposition:
         """(first owned global plane, number of owned planes) of ``rank`` (default: this rank); remainders go to the
         lowest ranks."""
         rank = self.rank if rank is None else int(rank)
+        if self.planes is not None:
+            if len(self.planes) != self.world or sum(self.planes) != int(nx):
+                raise ValueError(f"planes={self.planes}: need {self.world} counts that sum to nx = {nx}")
+            n = self.planes[rank]
+            if n < 2 and self.world > 1:
+                raise ValueError(f"slab of {n} plane(s) on rank {rank}: need at least 2 owned planes per rank")
+            return sum(self.planes[:rank]), n
         base, rem = divmod(int(nx), self.world)
         n = base + (1 if rank < rem else 0)
         x0 = rank * base + min(rank, rem)
@@ -84,6 +96,25 @@ class SlabDecomposition:
         grid.halo = 1
         grid.decomposition = self
         return grid
+
+
+def balanced_planes(plane_cost, world, min_planes=2):
+    """Owned planes per rank such that every rank gets about the same share of ``sum(plane_cost)`` (one relative cost per
+    global x plane).  Contiguous slabs, at least ``min_planes`` each; the cut after rank r is the first plane at which the
+    running cost reaches (r + 1) / world of the total."""
+    cost = np.asarray(plane_cost, dtype=np.float64).reshape(-1)
+    nx, world = cost.size, int(world)
+    if world < 1 or nx < world * min_planes or np.any(cost <= 0):
+        raise ValueError("balanced_planes: need positive costs and at least min_planes planes per rank")
+    acc = np.cumsum(cost)
+    cuts = [0]
+    for r in range(1, world):
+        x = int(np.searchsorted(acc, acc[-1] * r / world, side="left")) + 1
+        x = max(x, cuts[-1] + min_planes)          # room for this rank ...
+        x = min(x, nx - (world - r) * min_planes)  # ... and for the ones to come
+        cuts.append(x)
+    cuts.append(nx)
+    return [cuts[r + 1] - cuts[r] for r in range(world)]
 
 
 class HaloExchange:

@@ -13,13 +13,16 @@ def grid_factory(shape, compute_backend=None, velocity_set=None, backend_config=
     distributed example relies on that (examples/cfd/lid_driven_cavity_2d_distributed.py:22-27 calls the plain
     ``grid_factory``).  The equivalent here, one process per GPU: when ``torch.distributed`` is initialised with more than
     one rank, the grid returned is this rank's slab of ``shape`` (``SlabDecomposition.make_grid``).  ``backend_config={"slab":
-    False}`` asks for the whole block on this rank regardless."""
+    False}`` asks for the whole block on this rank regardless; ``{"slab_planes": [n_0, ..., n_{world-1}]}`` sets the owned planes
+    per rank (``xlb_b200.distribute.balanced_planes`` makes such a list from a per-plane cost)."""
     compute_backend = compute_backend or DefaultConfig.default_backend
     require_cuda_backend(compute_backend)
     from .cuda_grid import CudaGrid
 
     cfg = dict(backend_config or {})
     slab = cfg.pop("slab", "auto")
+    if not slab:
+        cfg.pop("slab_planes", None)
     if slab == "auto":
         import torch.distributed as dist
 
@@ -27,7 +30,7 @@ def grid_factory(shape, compute_backend=None, velocity_set=None, backend_config=
     if slab:
         from ..distribute import SlabDecomposition
 
-        return SlabDecomposition().make_grid(shape, backend_config=cfg)
+        return SlabDecomposition(planes=cfg.pop("slab_planes", None)).make_grid(shape, backend_config=cfg)
     return CudaGrid(shape, backend_config=cfg)
 
 
