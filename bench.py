@@ -577,6 +577,7 @@ def run_native(args):
     lattice, collision = run["lattice"], run["collision"]
     f_0, f_1, bc_mask, missing = run["fields"]
     t = run["t"]
+    slab_planes = run.get("planes")  # ``run`` is cleared before the strong-scaling leg
 
     # ---- optional: replay the step loop as CUDA graphs of --graph steps each (launch-bound small lattices)
     graphed, graph_lps = None, None
@@ -744,8 +745,8 @@ def run_native(args):
         "config": {
             "workload": workload, "lattice": lattice, "collision": collision, "policy": policy, "shape": list(shape), "omega": omega,
             "decomposition": f"x-slab x{world}" if world > 1 else "single block",
-            **({"slab_planes": run["planes"], "slab_balance": "planes per rank from a per-plane cost: cells + %.1f x half-way obstacle cells" % (HALFWAY_CELL_COST - 1.0)}
-               if run.get("planes") else {}),
+            **({"slab_planes": slab_planes, "slab_balance": "planes per rank from a per-plane cost: cells + %.1f x half-way obstacle cells" % (HALFWAY_CELL_COST - 1.0)}
+               if slab_planes else {}),
             **({"halo": halo_mode} if halo_mode else {}),
             **({"graph_steps": args.graph} if args.graph and world == 1 else {}),
             **({"buffers": "one population buffer, in-place AA pattern (xlb_step_inplace)"} if args.in_place else {}),

@@ -64,6 +64,10 @@ XLB_D void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
                  : "memory");
 }
 
+#ifndef XLB_TUNE_BULK_ROT
+#define XLB_TUNE_BULK_ROT 0
+#endif
+
 template <typename S, int Q, int TZ, bool HAS_BC>
 struct BulkLayout {
     static constexpr int HE = 16 / (int)sizeof(S);        // halo chunk, elements
@@ -117,8 +121,13 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
     });
 
     auto tile_coords = [&](int t, int& x, int& y, int& z0) {
-        const int xr = t / tiles_per_plane;
+        int xr = t / tiles_per_plane;
         const int r = t - xr * tiles_per_plane;
+#if XLB_TUNE_BULK_ROT
+        // claim order: the LAST plane first.  Inlet / outlet planes (x = 0, nx - 1) are the dear ones when their cells take the
+        // per-cell engine in this kernel; in plain order the outlet's tiles were the last ones claimed and formed the tail.
+        xr = xr == 0 ? p.n_planes - 1 : xr - 1;
+#endif
         const int yr = r / nseg;
         z0 = (r - yr * nseg) * TZ;
         y = p.y_begin + yr * p.y_stride;
