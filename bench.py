@@ -553,8 +553,10 @@ def run_native(args):
 
             planes = balanced_planes(obstacle_plane_cost(kind, shape, args.radius), world)
             run_slab = SlabDecomposition(rank=rank, world=world, planes=planes)
-        stepper, vs, pol, shape, omega = build_case(workload, slab=run_slab, shape=shape, variant=args.variant, radius=args.radius,
-                                                    backend_config={"in_place": True} if args.in_place else None)
+        cfg = {"in_place": True} if args.in_place else {}
+        if args.bc_cell_list != "auto":
+            cfg["bc_cell_list"] = args.bc_cell_list == "on"
+        stepper, vs, pol, shape, omega = build_case(workload, slab=run_slab, shape=shape, variant=args.variant, radius=args.radius, backend_config=cfg or None)
         if slab is not None:
             from xlb_b200.distribute import distribute
 
@@ -847,6 +849,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-overlap", action="store_true")
+    ap.add_argument("--bc-cell-list", default="auto", choices=["auto", "on", "off"], help="BC cell list (second, dense launch over the Zou-He / outflow cells): stepper default, forced on, forced off")
     ap.add_argument("--no-balance", action="store_true", help="N>1, obstacle workloads: equal plane counts per rank instead of equal cost")
     ap.add_argument("--halo", default="auto", choices=["auto", "peer", "nccl"], help="N>1: halo exchange fused into the edge launch over peer memory, or NCCL send/recv")
     ap.add_argument("--no-dist-graph", action="store_true", help="N>1: issue the distributed step eagerly instead of replaying its CUDA graph")

@@ -229,7 +229,12 @@ BULK_CASES = [
     cases.sphere3d((24, 16, 256), policy="FP64FP64", inlet="pressure"),
     cases.periodic((3, 3, 256), lattice="D3Q27", collision="KBC"),
     cases.cavity2d(0, shape=(20, 256), collision="KBC"),
-    cases.sphere3d((28, 16, 128)),  # D3Q27 KBC on a 128-wide grid: NT = 64 tiles
+    cases.sphere3d((28, 16, 128)),  # D3Q27 KBC on a 128-wide grid: tiles of two whole rows (multi-row mode of the 128-thread instance)
+    cases.sphere3d((28, 15, 128)),  # odd number of rows: one-row tiles of the 64-thread instance
+    cases.periodic((3, 4, 128), lattice="D3Q27", collision="KBC"),  # two-row tiles, every pull wraps in y and z somewhere
+    cases.periodic((2, 2, 128), lattice="D3Q27", collision="KBC"),  # ONE tile per plane: both source rows straddle the y boundary
+    cases.cavity3d(0, shape=(5, 6, 128), omega=1.7),  # D3Q19 BGK on two-row tiles
+    cases.cavity3d(0, shape=(4, 4, 128), omega=1.7, policy="FP64FP64"),
     # FP16 storage: packed-half2 consumer of the staged rows (512-cell tiles where nz allows, else 256)
     cases.cavity3d(0, shape=(4, 5, 512), omega=1.7, policy="FP32FP16"),
     cases.cavity3d(0, shape=(3, 4, 1024), omega=1.2, policy="FP32FP16"),

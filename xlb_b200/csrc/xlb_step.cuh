@@ -256,7 +256,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_c
             }
         }
     };
-#if !XLB_TUNE_K1_PHASED
+#if XLB_TUNE_K1_PHASED == 0
     if (HAS_BC) classify();
 #endif
 
@@ -273,7 +273,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_c
     const int z_hi = (tz == p.ntz - 1) ? 0 : z0 + V;  // source of the element right of my vector
     T f[Q][V];
     const S* pl = f0;
-#if XLB_TUNE_K1_PHASED
+#if XLB_TUNE_K1_PHASED == 1
     // phase 1: issue every population's vector load before anything waits on one.  With the classification of tagged cells in
     // front of the loads, and the exit of inactive lanes between the z-shifted populations and the rest, a thread made three
     // dependent round trips to DRAM (ids -> shifted populations -> the others; ncu source page)
@@ -339,11 +339,18 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_c
         pl += p.qs;
     });
 #endif
+#if XLB_TUNE_K1_PHASED == 2
+    // mode 2: the original interleaved load / shift loop, but the ids are looked at only now, and inactive lanes (last block only)
+    // leave just before the stores -- an exit here lets the compiler sink the loads that need no shuffle below it
+    if (HAS_BC) classify();
+#else
     if (!active) return;
+#endif
 
     if (HAS_BC && slow) {
         // a BC kind that needs f_pre / missing_mask / neighbour gathers: per-cell generic engine
-        for (int j = 0; j < V; ++j) cell_update_generic<T, S, Q, COLL>(p, x, y, z0 + j);
+        if (active)
+            for (int j = 0; j < V; ++j) cell_update_generic<T, S, Q, COLL>(p, x, y, z0 + j);
         return;
     }
     if constexpr (HAS_BC && HALF) {
@@ -403,6 +410,9 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_c
         });
     }
     // ---- one aligned vector store per population (+ the halo push of the populations that leave the slab here)
+#if XLB_TUNE_K1_PHASED == 2
+    if (!active) return;
+#endif
     S* ql = f1 + cell;
     PeerDst<S> pd{nullptr, 0, 0};
     if constexpr (PUSH) pd = peer_dst<S, Q>(p, x, y, (long long)y * p.nz + z0);

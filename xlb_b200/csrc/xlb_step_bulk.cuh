@@ -65,7 +65,7 @@ XLB_D void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
 }
 
 #ifndef XLB_TUNE_BULK_ROT
-#define XLB_TUNE_BULK_ROT 0
+#define XLB_TUNE_BULK_ROT 1
 #endif
 
 template <typename S, int Q, int TZ, bool HAS_BC>
@@ -104,8 +104,12 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
     S* __restrict__ f1 = static_cast<S*>(p.f1);
     const int tid = threadIdx.x;
     const int lane = tid & 31;
-    const int nseg = p.nz / TZ;
-    const int tiles_per_plane = p.n_rows * nseg;
+    // multi-row tiles: on rows of exactly NT cells (nz == NT, e.g. the 128-wide BASELINE configs[2]) a tile is C whole,
+    // consecutive rows -- thread t owns cell z = t of each -- so that the bulk copies are C rows long where the source rows are
+    // adjacent in memory and the per-tile costs (copy issue, barrier, claim) are paid per C * NT cells like on wide rows
+    const bool multi = !H2 && C > 1 && p.nz == NT;
+    const int nseg = multi ? 1 : p.nz / TZ;
+    const int tiles_per_plane = multi ? p.n_rows / C : p.n_rows * nseg;
     const int total = p.n_planes * tiles_per_plane;  // < 2^31, checked on the host
     const long long plane = (long long)p.ny * p.nz;
 
@@ -128,8 +132,8 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
         // per-cell engine in this kernel; in plain order the outlet's tiles were the last ones claimed and formed the tail.
         xr = xr == 0 ? p.n_planes - 1 : xr - 1;
 #endif
-        const int yr = r / nseg;
-        z0 = (r - yr * nseg) * TZ;
+        const int yr = multi ? r * C : r / nseg;
+        z0 = multi ? 0 : (r - yr * nseg) * TZ;
         y = p.y_begin + yr * p.y_stride;
         x = p.x_begin + xr * p.x_stride;
     };
@@ -157,7 +161,11 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
             const S* row = f0 + lane * p.qs + (xs * plane + (long long)ys * p.nz);
             S* dst = reinterpret_cast<S*>(stage) + lane * L::ROW;
             const bool first = z0 == 0, last = z0 + TZ == p.nz;
-            if (lcz == 0 || one_seg) {
+            if (multi && ys + C > p.ny) {  // the C source rows straddle the periodic y boundary: one copy per row
+#pragma unroll
+                for (int r = 0; r < C; ++r)
+                    bulk_g2s(dst + HE + r * NT, f0 + lane * p.qs + (xs * plane + (long long)wrap1(y + r - lcy, p.ny) * p.nz), NT * sizeof(S), &full[s]);
+            } else if (lcz == 0 || one_seg) {
                 bulk_g2s(dst + HE, row + z0, TZ * sizeof(S), &full[s]);
             } else if (lcz == 1) {  // pull from z-1: HE elements left of the segment (periodic)
                 if (MERGE && !first) {
@@ -388,8 +396,13 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
 #pragma unroll
             for (int j = 0; j < C; ++j) {
                 int idx = tid + j * NT - cz;
-                if (cz == 1 && j == 0) idx = (one_seg && idx < 0) ? TZ - 1 : idx;           // z = 0 pulls from z = nz - 1
-                if (cz == -1 && j == C - 1) idx = (one_seg && idx == TZ) ? 0 : idx;         // z = nz - 1 pulls from z = 0
+                if (multi) {  // row j of the tile, periodic within the row
+                    if (cz == 1 && tid == 0) idx = j * NT + NT - 1;
+                    if (cz == -1 && tid == NT - 1) idx = j * NT;
+                } else {
+                    if (cz == 1 && j == 0) idx = (one_seg && idx < 0) ? TZ - 1 : idx;           // z = 0 pulls from z = nz - 1
+                    if (cz == -1 && j == C - 1) idx = (one_seg && idx == TZ) ? 0 : idx;         // z = nz - 1 pulls from z = 0
+                }
                 f[l][j] = to_compute<T, S>(pops[l * L::ROW + HE + idx]);
             }
         });
@@ -434,7 +447,10 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
         }
         const int zc = z0 + tid;
         if (HAS_BC && slow) {
-            for (int j = 0; j < C; ++j) cell_update_generic<T, S, Q, COLL>(p, x, y, zc + j * NT);
+            for (int j = 0; j < C; ++j) {
+                if (multi) cell_update_generic<T, S, Q, COLL>(p, x, y + j, zc);
+                else cell_update_generic<T, S, Q, COLL>(p, x, y, zc + j * NT);
+            }
             flush_claim();
             continue;
         }

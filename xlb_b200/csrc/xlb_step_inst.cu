@@ -83,6 +83,10 @@ static int launch_vector(const StepParams& p0, cudaStream_t st) {
 #define XLB_TUNE_HBMINB 3
 #endif
 
+#ifndef XLB_TUNE_MULTIROW
+#define XLB_TUNE_MULTIROW 1
+#endif
+
 template <typename T, typename S, int Q, int COLL, int C, int NT, bool HAS_BC, bool HALF = false, bool H2 = false>
 static int launch_bulk(const StepParams& p, cudaStream_t st) {
     constexpr int TZ = NT * C;
@@ -113,7 +117,8 @@ static int launch_bulk(const StepParams& p, cudaStream_t st) {
         blocks_per_sm = cached_blocks[slot];
         n_sm = cached_sms[slot];
     }
-    const long long total = (long long)p.n_planes * p.n_rows * (p.nz / TZ);
+    const bool multi = !H2 && C > 1 && p.nz == NT;  // multi-row tiles (xlb_step_bulk.cuh): C rows of NT cells per tile
+    const long long total = multi ? (long long)p.n_planes * (p.n_rows / C) : (long long)p.n_planes * p.n_rows * (p.nz / TZ);
     if (total >= (1ll << 30)) return -1000;  // tile indices are 32-bit in the kernel
     long long grid = (long long)blocks_per_sm * n_sm;
     if (grid > total) grid = total;
@@ -140,7 +145,11 @@ static int try_bulk(const StepParams& p, cudaStream_t st) {
     if (p.nz % (XLB_TUNE_NT * C) == 0) return launch_bulk<T, S, Q, COLL, C, XLB_TUNE_NT, HAS_BC, HALF>(p, st);
 #else
     if (p.nz % (128 * C) == 0) return launch_bulk<T, S, Q, COLL, C, 128, HAS_BC, HALF>(p, st);
-    if constexpr (Q == 27 && COLL == XLB_KBC) {  // narrow grids (BASELINE config 3 is 128 cells wide)
+#if XLB_TUNE_MULTIROW
+    // rows of exactly 128 cells (BASELINE configs[2] is 128 wide): tiles of C whole rows on the 128-thread instance
+    if (C > 1 && p.nz == 128 && p.n_rows % C == 0 && p.y_stride == 1) return launch_bulk<T, S, Q, COLL, C, 128, HAS_BC, HALF>(p, st);
+#endif
+    if constexpr (Q == 27 && COLL == XLB_KBC) {  // narrow grids
         if (p.nz % (64 * C) == 0) return launch_bulk<T, S, Q, COLL, C, 64, HAS_BC, HALF>(p, st);
     }
 #endif
