@@ -89,24 +89,30 @@ class ClockSampler:
         self.index = index
         self.rows = []
         self._stop = threading.Event()
+        self._spawned = threading.Event()
         self._t = None
 
     def _run(self):
         while not self._stop.is_set():
             try:
-                out = subprocess.run(
+                proc = subprocess.Popen(
                     ["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits", "-i", str(self.index)],
-                    capture_output=True, text=True, timeout=5,
-                ).stdout.strip()
+                    stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True,
+                )
+                self._spawned.set()
+                out = proc.communicate(timeout=5)[0].strip()
                 if out:
                     self.rows.append([c.strip() for c in out.split(",")])
             except Exception:
-                pass
+                self._spawned.set()
             self._stop.wait(0.2)
 
     def start(self):
+        """Returns once the first nvidia-smi process exists: creating it (a fork of this process, with the GIL held) must not
+        fall between the start event and the first launch of the timed region; the query itself then runs during the region."""
         self._t = threading.Thread(target=self._run, daemon=True)
         self._t.start()
+        self._spawned.wait(timeout=5)
 
     def stop(self):
         self._stop.set()

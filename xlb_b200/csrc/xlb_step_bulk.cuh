@@ -86,8 +86,9 @@ struct BulkLayout {
 
 // H2 (FP16 storage only): the staged rows are read as packed half2 words -- thread t owns the cell pairs
 // (2t, 2t+1) + k*2*NT of the tile -- and stay packed in registers (PackedH2, see xlb_step_h2.cuh) through the collision.
-template <typename T, typename S, int Q, int COLL, int C, int NT, int STAGES, int MINB, bool HAS_BC, bool HALF = false, bool H2 = false>
+template <typename T, typename S, int Q, int COLL, int C, int NT, int STAGES, int MINB, bool HAS_BC, bool HALF = false, bool H2 = false, bool MULTI = false>
 __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_constant__ StepParams p) {
+    static_assert(!MULTI || (!H2 && C > 1), "multi-row tiles: C > 1 rows per tile, not for the packed-half2 consumer");
     static_assert(!H2 || (std::is_same<S, __half>::value && std::is_same<T, float>::value && C % 2 == 0), "H2: FP32 compute, FP16 storage, even C");
     constexpr int TZ = NT * C;
     using L = BulkLayout<S, Q, TZ, HAS_BC>;
@@ -107,7 +108,8 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
     // multi-row tiles: on rows of exactly NT cells (nz == NT, e.g. the 128-wide BASELINE configs[2]) a tile is C whole,
     // consecutive rows -- thread t owns cell z = t of each -- so that the bulk copies are C rows long where the source rows are
     // adjacent in memory and the per-tile costs (copy issue, barrier, claim) are paid per C * NT cells like on wide rows
-    const bool multi = !H2 && C > 1 && p.nz == NT;
+    // A template flag, not a run-time test: as a run-time test it cost the wide-row instances 2.5 % (profiles/r2v_bench_default.json).
+    constexpr bool multi = MULTI;  // the host launches this instance only when p.nz == NT
     const int nseg = multi ? 1 : p.nz / TZ;
     const int tiles_per_plane = multi ? p.n_rows / C : p.n_rows * nseg;
     const int total = p.n_planes * tiles_per_plane;  // < 2^31, checked on the host

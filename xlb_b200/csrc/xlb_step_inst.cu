@@ -87,14 +87,14 @@ static int launch_vector(const StepParams& p0, cudaStream_t st) {
 #define XLB_TUNE_MULTIROW 1
 #endif
 
-template <typename T, typename S, int Q, int COLL, int C, int NT, bool HAS_BC, bool HALF = false, bool H2 = false>
+template <typename T, typename S, int Q, int COLL, int C, int NT, bool HAS_BC, bool HALF = false, bool H2 = false, bool MULTI = false>
 static int launch_bulk(const StepParams& p, cudaStream_t st) {
     constexpr int TZ = NT * C;
     constexpr int STAGES = H2 ? XLB_TUNE_HSTAGES : XLB_TUNE_STAGES;
     using L = BulkLayout<S, Q, TZ, HAS_BC>;
     constexpr int BM0 = H2 ? XLB_TUNE_HBMINB : XLB_TUNE_BMINB;
     constexpr int BMINB = (BM0 * 128 / NT) > 0 ? (BM0 * 128 / NT) : 1;  // same register budget per thread for every NT
-    auto kern = step_bulk_kernel<T, S, Q, COLL, C, NT, STAGES, BMINB, HAS_BC, HALF, H2>;
+    auto kern = step_bulk_kernel<T, S, Q, COLL, C, NT, STAGES, BMINB, HAS_BC, HALF, H2, MULTI>;
     // the shared-memory opt-in and the occupancy are per device: cached per device ordinal (one slot each, filled under a lock)
     constexpr int MAX_DEV = 64;
     static std::mutex mu;
@@ -117,7 +117,8 @@ static int launch_bulk(const StepParams& p, cudaStream_t st) {
         blocks_per_sm = cached_blocks[slot];
         n_sm = cached_sms[slot];
     }
-    const bool multi = !H2 && C > 1 && p.nz == NT;  // multi-row tiles (xlb_step_bulk.cuh): C rows of NT cells per tile
+    constexpr bool multi = MULTI;  // multi-row tiles (xlb_step_bulk.cuh): C rows of NT cells per tile, p.nz == NT
+    if (multi && (p.nz != NT || p.n_rows % C != 0 || p.y_stride != 1)) return -1000;
     const long long total = multi ? (long long)p.n_planes * (p.n_rows / C) : (long long)p.n_planes * p.n_rows * (p.nz / TZ);
     if (total >= (1ll << 30)) return -1000;  // tile indices are 32-bit in the kernel
     long long grid = (long long)blocks_per_sm * n_sm;
@@ -147,7 +148,9 @@ static int try_bulk(const StepParams& p, cudaStream_t st) {
     if (p.nz % (128 * C) == 0) return launch_bulk<T, S, Q, COLL, C, 128, HAS_BC, HALF>(p, st);
 #if XLB_TUNE_MULTIROW
     // rows of exactly 128 cells (BASELINE configs[2] is 128 wide): tiles of C whole rows on the 128-thread instance
-    if (C > 1 && p.nz == 128 && p.n_rows % C == 0 && p.y_stride == 1) return launch_bulk<T, S, Q, COLL, C, 128, HAS_BC, HALF>(p, st);
+    if constexpr (C > 1) {
+        if (p.nz == 128 && p.n_rows % C == 0 && p.y_stride == 1) return launch_bulk<T, S, Q, COLL, C, 128, HAS_BC, HALF, false, true>(p, st);
+    }
 #endif
     if constexpr (Q == 27 && COLL == XLB_KBC) {  // narrow grids
         if (p.nz % (64 * C) == 0) return launch_bulk<T, S, Q, COLL, C, 64, HAS_BC, HALF>(p, st);
@@ -232,8 +235,10 @@ static int step_main(const StepParams& p, int variant, cudaStream_t st) {
     const bool vec_ok = (p.nz % VMAX == 0) && (p.qs % VMAX == 0) && (a0 % (VMAX * sizeof(S)) == 0) && (a1 % (VMAX * sizeof(S)) == 0) &&
                         masks_ok(VMAX);
     if (variant == XLB_VARIANT_VECTOR && !vec_ok && !(VMAX == 8 && p.nz % 4 == 0)) return set_error(XLB_EALIGN, "xlb_step: vector variant needs nz, q_stride and base pointers aligned to the vector width");
-    // AUTO: the bulk-staged pipeline where the B200 sweeps show it ahead of the vector kernel (D3Q27 KBC, compute-heavy)
-    if constexpr (Q == 27 && COLL == XLB_KBC && sizeof(S) == 4) {
+    // AUTO: the bulk-staged pipeline where the B200 measurements show it ahead of the vector kernel: D3Q27 with 4-byte storage,
+    // KBC (compute-heavy) and BGK (384x256x512: 30.4k vs 28.2k MLUPS, profiles/r2u_bench_more.jsonl).  D3Q19 stays on the
+    // vector kernel (512^3: 42.4k vs 40.9k; 128^3 equal).
+    if constexpr (Q == 27 && (COLL == XLB_KBC || COLL == XLB_BGK) && sizeof(S) == 4) {
         // (round 1 fell back to the vector kernel on blocks where a half-way obstacle covers more than ~1 % of the cells; with the
         // dynamic tile scheduler and the packed missing bits the pipeline is ahead there too: 22.7k vs 21.1k MLUPS on a
         // 192x1536x1536 block holding half of an r = 192 sphere)
