@@ -159,3 +159,26 @@ def test_oracle_ring_equals_global_stream(lattice, shape, n):
     lat = make_lattice(lattice)
     f = np.random.default_rng(1).uniform(0, 1, (lat.q,) + shape)
     assert np.array_equal(sharded_stream(lat, f, n), ops.stream(lat, f))
+
+
+def test_bench_plane_cost_follows_the_obstacle_of_its_workloads():
+    """bench.py hands the ranks of an obstacle workload slabs of equal COST: its per-plane cost must count the same sphere
+    bench.build_case tags (same centre, same radius), and the resulting slabs must be lighter where the sphere is."""
+    import bench
+    from xlb_b200.distribute import balanced_planes
+
+    for kind, shape in (("windtunnel", (256, 96, 96)), ("sphere", (240, 96, 96))):
+        nx, ny, nz = shape
+        r, cx = (min(ny // 8, nx // 4), nx // 3) if kind == "windtunnel" else (ny // 12, nx // 6)
+        cy, cz = ny // 2, nz // 2
+        y, z = np.meshgrid(np.arange(ny), np.arange(nz), indexing="ij")
+        solid = np.array([np.count_nonzero((x - cx) ** 2 + (y - cy) ** 2 + (z - cz) ** 2 < r * r) for x in range(nx)])
+        cost = bench.obstacle_plane_cost(kind, shape)
+        assert cost.shape == (nx,) and np.all(cost >= ny * nz)
+        extra = (cost - ny * nz) / (bench.HALFWAY_CELL_COST - 1.0)  # the model's solid cells per plane (pi * (r^2 - t^2))
+        assert np.array_equal(extra > 0, solid > 0) or np.count_nonzero((extra > 0) != (solid > 0)) <= 2  # same planes, up to the two tips
+        assert abs(extra.sum() - solid.sum()) <= 0.05 * solid.sum()
+        planes = balanced_planes(cost, 8)
+        cuts = np.cumsum([0] + planes)
+        holder = int(np.searchsorted(cuts, cx, side="right") - 1)  # the rank that holds the sphere's centre plane
+        assert planes[holder] == min(planes) and sum(planes) == nx
