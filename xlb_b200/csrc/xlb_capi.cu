@@ -140,7 +140,9 @@ int xlb_step_ex(const XlbDomain* dom, int collision, const XlbCollisionParams* c
 int xlb_step_range(const XlbDomain* dom, int collision, const XlbCollisionParams* cp, const XlbStepRange* range, const XlbHaloPush* halo,
                    const void* f0, void* f1, const uint8_t* bc_mask, const uint8_t* missing_mask, const XlbBcEntry* bc_table, int n_bc,
                    double omega, int timestep, int variant, void* stream) {
-    (void)timestep;  // carried for signature parity with nse_stepper.py:229; the JAX path never reads it
+    // ``timestep`` (nse_stepper.py:229; the JAX path never reads it) only chooses the ORDER in which the planes are walked: odd
+    // steps go from the last plane to the first.  The planes a step wrote last are the ones still in the 126 MB L2; the next
+    // step reads them first instead of evicting them before it gets there.  Results do not depend on the order.
     if (int rc = check_domain(dom, "xlb_step")) return rc;
     if (!f0 || !f1) return set_error(XLB_EINVAL, "xlb_step: null population pointer");
     if (f0 == f1) return set_error(XLB_EINVAL, "xlb_step: f0 and f1 must be distinct buffers (pull scheme, double buffered)");
@@ -172,6 +174,7 @@ int xlb_step_range(const XlbDomain* dom, int collision, const XlbCollisionParams
     p.ny = dom->ny;
     p.nz = dom->nz;
     p.x_begin = r.x_begin;
+    p.reverse = timestep & 1;
     p.x_end = x_last + 1;
     p.x_stride = r.x_stride;
     p.n_planes = r.n_planes;
@@ -267,6 +270,7 @@ int xlb_step_inplace(const XlbDomain* dom, int collision, const XlbCollisionPara
     p.bct = has_bc ? bc_table : nullptr;
     p.nx = dom->nx, p.ny = dom->ny, p.nz = dom->nz;
     p.x_begin = 0, p.x_end = dom->nx, p.x_stride = 1, p.n_planes = dom->nx;
+    p.reverse = parity;  // the L step walks the planes backwards: what the P step wrote last is read first (L2)
     p.y_begin = 0, p.y_stride = 1, p.n_rows = dom->ny;
     p.x_periodic = 1;
     const long long ncell = (long long)dom->nx * dom->ny * dom->nz;

@@ -137,6 +137,46 @@ XLB_D Vec<S, V> ld_vec(const S* p) { return *reinterpret_cast<const Vec<S, V>*>(
 template <typename S, int V>
 XLB_D void st_vec(S* p, const Vec<S, V>& x) { *reinterpret_cast<Vec<S, V>*>(p) = x; }
 
+// ---- population loads / stores with an L2 eviction policy (XLB_TUNE_L2HINT: bit 0 stores evict_last, bit 1 loads evict_first).
+// What a step writes is what the next step reads; what it reads is dead.  On lattices of the order of the 126 MB L2 the written
+// lines should outlive the read ones.  16-byte accesses only (the widths the fused kernels use); other widths take the plain path.
+#ifndef XLB_TUNE_L2HINT
+#define XLB_TUNE_L2HINT 0
+#endif
+XLB_D uint64_t l2_policy_evict_last() {
+    uint64_t pol;
+    asm("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+XLB_D uint64_t l2_policy_evict_first() {
+    uint64_t pol;
+    asm("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+template <typename S, int V>
+XLB_D Vec<S, V> ld_pop(const S* p, uint64_t pol) {
+    if constexpr ((XLB_TUNE_L2HINT & 2) && sizeof(S) * V == 16) {
+        uint32_t a, b, c, d;
+        asm("ld.global.L2::cache_hint.v4.u32 {%0, %1, %2, %3}, [%4], %5;" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "l"(p), "l"(pol));
+        Vec<S, V> r;
+        uint32_t w[4] = {a, b, c, d};
+        memcpy(&r, w, 16);
+        return r;
+    } else {
+        return ld_vec<S, V>(p);
+    }
+}
+template <typename S, int V>
+XLB_D void st_pop(S* p, const Vec<S, V>& x, uint64_t pol) {
+    if constexpr ((XLB_TUNE_L2HINT & 1) && sizeof(S) * V == 16) {
+        uint32_t w[4];
+        memcpy(w, &x, 16);
+        asm volatile("st.global.L2::cache_hint.v4.u32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(p), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]), "l"(pol) : "memory");
+    } else {
+        st_vec<S, V>(p, x);
+    }
+}
+
 XLB_D float shfl_up1(float v) { return __shfl_up_sync(0xffffffffu, v, 1); }
 XLB_D double shfl_up1(double v) { return __shfl_up_sync(0xffffffffu, v, 1); }
 XLB_D __half shfl_up1(__half v) { return __shfl_up_sync(0xffffffffu, v, 1); }
@@ -173,6 +213,7 @@ struct StepParams {
     int x_stride, n_planes;
     int y_begin, y_stride, n_rows;  // rows updated in each plane: y_begin + k * y_stride, k < n_rows (whole planes: 0, 1, ny)
     int x_periodic;
+    int reverse;  // 1: walk the planes from the last to the first (odd time steps; see xlb_step_range)
     int ntz;  // nz / V
     int ntz_shift;  // log2(ntz) when ntz is a power of two, else -1
     long long qs;   // population stride (elements)
@@ -200,6 +241,18 @@ struct StepParams {
 
 // slab axis of the multi-GPU decomposition in kernel axes: x for the 3-D lattices, y (= user x) for D2Q9, whose fields
 // run as nx = 1
+#ifndef XLB_TUNE_REVERSE
+#define XLB_TUNE_REVERSE 1
+#endif
+// k-th plane of a launch in the order the grid walks them (StepParams.reverse)
+XLB_D int plane_index(const StepParams& p, int k) {
+#if XLB_TUNE_REVERSE
+    return p.reverse ? p.n_planes - 1 - k : k;
+#else
+    return k;
+#endif
+}
+
 template <int Q>
 XLB_HD constexpr int slab_axis() { return Q == 9 ? 1 : 0; }
 

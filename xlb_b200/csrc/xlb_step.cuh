@@ -144,7 +144,7 @@ __global__ void __launch_bounds__(128) step_generic_kernel(const __grid_constant
     const long long row = (long long)p.n_rows * p.nz;
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= row) return;
-    const int x = p.x_begin + blockIdx.y * p.x_stride;
+    const int x = p.x_begin + plane_index(p, blockIdx.y) * p.x_stride;
     cell_update_generic_impl<T, S, Q, COLL>(p, x, p.y_begin + (int)(i / p.nz) * p.y_stride, (int)(i % p.nz));
 }
 
@@ -207,7 +207,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_c
     int i = blockIdx.x * BLOCK + threadIdx.x;
     const bool active = i < nvec;
     if (!active) i = nvec - 1;  // keep the lane alive for the shuffles
-    const int x = p.x_begin + blockIdx.y * p.x_stride;
+    const int x = p.x_begin + plane_index(p, blockIdx.y) * p.x_stride;
     int y, tz;
     if (p.ntz_shift >= 0) {
         y = i >> p.ntz_shift;
@@ -273,6 +273,9 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_c
     const int z_hi = (tz == p.ntz - 1) ? 0 : z0 + V;  // source of the element right of my vector
     T f[Q][V];
     const S* pl = f0;
+    uint64_t pol_ld = 0, pol_st = 0;
+    if constexpr ((XLB_TUNE_L2HINT & 2) != 0) pol_ld = l2_policy_evict_first();
+    if constexpr ((XLB_TUNE_L2HINT & 1) != 0) pol_st = l2_policy_evict_last();
 #if XLB_TUNE_K1_PHASED == 1
     // phase 1: issue every population's vector load before anything waits on one.  With the classification of tagged cells in
     // front of the loads, and the exit of inactive lanes between the z-shifted populations and the rest, a thread made three
@@ -321,7 +324,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_c
         const long long ox = D::cx == 0 ? ox0 : (D::cx == 1 ? oxm : oxp);
         const int oy = D::cy == 0 ? oy0 : (D::cy == 1 ? oym : oyp);
         const S* row = pl + (ox + oy);
-        const Vec<S, V> v = ld_vec<S, V>(row + z0);
+        const Vec<S, V> v = ld_pop<S, V>(row + z0, pol_ld);
         if (D::cz == 0) {
 #pragma unroll
             for (int j = 0; j < V; ++j) f[l][j] = to_compute<T, S>(v.v[j]);
@@ -422,7 +425,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_kernel(const __grid_c
         Vec<S, V> o;
 #pragma unroll
         for (int j = 0; j < V; ++j) o.v[j] = to_store<S, T>(f[l][j]);
-        st_vec<S, V>(ql, o);
+        st_pop<S, V>(ql, o, pol_st);
         ql += p.qs;
         if constexpr (PUSH) {
             constexpr int ca = slab_c<Q>(Dir<Q, l>::cx, Dir<Q, l>::cy);

@@ -134,6 +134,11 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
         // per-cell engine in this kernel; in plain order the outlet's tiles were the last ones claimed and formed the tail.
         xr = xr == 0 ? p.n_planes - 1 : xr - 1;
 #endif
+#if XLB_TUNE_REVERSE
+        // odd time steps walk the planes backwards (StepParams.reverse), keeping the two dear planes in front:
+        // [n-1, 0, 1, ..., n-2] becomes [0, n-1, n-2, ..., 1]
+        if (p.reverse) xr = p.n_planes - 1 - xr;
+#endif
         const int yr = multi ? r * C : r / nseg;
         z0 = multi ? 0 : (r - yr * nseg) * TZ;
         y = p.y_begin + yr * p.y_stride;

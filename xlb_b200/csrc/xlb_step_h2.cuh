@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) step_vector_h2_kernel(const __gri
     int i = blockIdx.x * BLOCK + threadIdx.x;
     const bool active = i < nvec;
     if (!active) i = nvec - 1;
-    const int x = p.x_begin + blockIdx.y * p.x_stride;
+    const int x = p.x_begin + plane_index(p, blockIdx.y) * p.x_stride;
     int y, tz;
     if (p.ntz_shift >= 0) {
         y = i >> p.ntz_shift;
