@@ -64,6 +64,9 @@ XLB_D void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
                  : "memory");
 }
 
+#ifndef XLB_TUNE_BULK_REVERSE
+#define XLB_TUNE_BULK_REVERSE 0  // the backwards walk of odd steps (StepParams.reverse) pays in K1 / K1c / K1d; here it is neutral on wide lattices and costs configs[2] 1.7 % (profiles/r3a_sweep_bulk_reverse.log)
+#endif
 #ifndef XLB_TUNE_BULK_ROT
 #define XLB_TUNE_BULK_ROT 1
 #endif
@@ -134,7 +137,7 @@ __global__ void __launch_bounds__(NT, MINB) step_bulk_kernel(const __grid_consta
         // per-cell engine in this kernel; in plain order the outlet's tiles were the last ones claimed and formed the tail.
         xr = xr == 0 ? p.n_planes - 1 : xr - 1;
 #endif
-#if XLB_TUNE_REVERSE
+#if XLB_TUNE_BULK_REVERSE
         // odd time steps walk the planes backwards (StepParams.reverse), keeping the two dear planes in front:
         // [n-1, 0, 1, ..., n-2] becomes [0, n-1, n-2, ..., 1]
         if (p.reverse) xr = p.n_planes - 1 - xr;
