@@ -514,3 +514,35 @@ def test_graphed_steps_equal_eager_loop(case):
     assert torch.equal(a, g_0)
     with pytest.raises(ValueError):
         GraphedSteps(st, f_0, f_1, bc_mask, missing, case["omega"], steps=3)
+
+
+PLANE_ORDER_CASES = [
+    (cases.cavity3d(0, shape=(9, 6, 128), omega=1.7), "VARIANT_AUTO"),  # K1 (vector)
+    (cases.cavity3d(0, shape=(7, 5, 256), omega=1.7, policy="FP32FP16"), "VARIANT_AUTO"),  # K1c (packed half2)
+    (cases.cavity3d(0, shape=(6, 4, 256), omega=1.7, policy="FP64FP64"), "VARIANT_AUTO"),
+    (cases.sphere3d((28, 16, 256)), "VARIANT_AUTO"),  # K1b (bulk pipeline: keeps its own claim order)
+    (cases.sphere3d((28, 16, 128)), "VARIANT_VECTOR"),
+    (cases.cavity2d(0, shape=(20, 64), omega=1.6), "VARIANT_AUTO"),
+]
+
+
+@pytest.mark.parametrize("case,variant", PLANE_ORDER_CASES, ids=lambda v: v["name"] if isinstance(v, dict) else v)
+def test_timestep_parity_only_changes_the_plane_order(case, variant):
+    """``timestep`` is carried for signature parity with nse_stepper.py:229 and the reference never reads it; here its parity
+    chooses the direction in which the fused kernels walk the planes (L2 reuse between steps).  The result
+    must not depend on it: even and odd time steps from the same state are bitwise equal, full launches and plane sub-ranges."""
+    st, _ = build_product(case, backend_config={"kernel_variant": getattr(_lib, variant)})
+    f_0, f_1, bc_mask, missing = st.prepare_fields()
+    f_0.copy_(to_dev(cases.random_state(case, seed=9)))
+    outs = []
+    for timestep in (0, 1, 7):
+        f_1.zero_()
+        st(f_0, f_1, bc_mask, missing, case["omega"], timestep)
+        outs.append(f_1.clone())
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+    if len(case["shape"]) == 3:
+        nx = case["shape"][0]
+        f_1.zero_()
+        for xb, xe in [(0, 2), (2, nx - 1), (nx - 1, nx)]:
+            st.launch_range(f_0, f_1, bc_mask, missing, case["omega"], 1, xb, xe)
+        assert torch.equal(f_1, outs[0])
