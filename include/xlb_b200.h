@@ -127,7 +127,10 @@ long long xlb_launch_count(void);
 
 /* IncompressibleNavierStokesStepper.__call__  (nse_stepper.py:227-282 JAX pull; :427-476 Warp kernel)
  * f1[:, x_begin:x_end] = collide(bc(stream(f0)))  -- one fused launch.  bc_table/bc_mask/missing_mask
- * may be NULL when n_bc == 0 (fully periodic). */
+ * may be NULL when n_bc == 0 (fully periodic).
+ * ``timestep`` is the reference's argument of the same name (nse_stepper.py:229; its JAX path never reads it).  The result does
+ * not depend on it; its parity only selects the order in which the launch walks the planes (odd: last to first), so that a
+ * step starts on the planes the previous step wrote last, which are the ones still in the L2. */
 int xlb_step(const XlbDomain* dom, int collision, const void* f0, void* f1, const uint8_t* bc_mask,
              const uint8_t* missing_mask, const XlbBcEntry* bc_table, int n_bc, double omega, int timestep,
              int x_begin, int x_end, int variant, void* stream);
